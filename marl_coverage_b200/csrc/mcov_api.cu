@@ -1,0 +1,507 @@
+// mcov_api.cu — extern "C" boundary of libmcov_b200.so (see include/mcov.h).
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+#include "mcov_internal.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    return fail(MCOV_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+inline bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+int64_t align_up64(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+int obs_channels(const mcov_config& c) {
+    if (c.env_type == MCOV_ENV_SUPER) return c.use_scanning ? 4 : c.num_robots + 3;
+    int layers = c.mini_map_rad > 0 ? 5 : 3;          // dec_grid_rl.py:322-332
+    if (c.dist_reward) layers += 1;
+    if (c.dijkstra_input) layers += 1;
+    return layers;
+}
+
+// ---- map packer --------------------------------------------------------------------------------
+// One thread per output word; 32 cells along y.  cells: int8 [n][W][L]; output geometry is
+// (W + 2b, L + 2b) with b = add_border (obstacle ring, dec_grid_rl.py:471-472).
+__global__ void pack_maps_kernel(const int8_t* __restrict__ cells, int n_maps, int W, int L, int b,
+                                 int strips, int Wp, uint32_t* __restrict__ wall,
+                                 uint32_t* __restrict__ pos) {
+    const int PW = strips * Wp;
+    const long long total = (long long)n_maps * PW;
+    const int Wo = W + 2 * b, Lo = L + 2 * b;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int m = (int)(t / PW);
+        const int w = (int)(t % PW);
+        const int s = w / Wp, x = w % Wp;
+        uint32_t wb = 0, pb = 0;
+        if (x < Wo) {
+            for (int k = 0; k < 32; ++k) {
+                const int y = s * 32 + k;
+                if (y >= Lo) break;
+                int v = -1;                                           // border cell
+                const int xi = x - b, yi = y - b;
+                if (xi >= 0 && xi < W && yi >= 0 && yi < L) v = cells[((size_t)m * W + xi) * L + yi];
+                wb |= (uint32_t)(v < 0) << k;
+                pb |= (uint32_t)(v > 0) << k;
+            }
+        }
+        wall[t] = wb;
+        pos[t] = pb;
+    }
+}
+
+__global__ void count_free_kernel(const uint32_t* __restrict__ pos, int n_maps, int PW, int32_t* out) {
+    __shared__ int red[32];
+    const int m = blockIdx.x;
+    int c = 0;
+    for (int w = threadIdx.x; w < PW; w += blockDim.x) c += __popc(pos[(size_t)m * PW + w]);
+    for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int s = 0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) s += red[k];
+        out[m] = s;
+    }
+}
+
+int check_ready(const mcov_env* env) {
+    if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
+    if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+    if (!env->bound) return fail(MCOV_ERR_STATE, "mcov_bind_state has not been called");
+    return MCOV_OK;
+}
+
+void fill_dec_params(mcov_env* env, mcov::DecParams& p) {
+    const mcov_config& c = env->cfg;
+    const mcov_layout& l = env->lay;
+    memset(&p, 0, sizeof(p));
+    p.E = c.num_envs;
+    p.N = c.num_robots;
+    p.g = env->g;
+    p.R = c.sensor_range;
+    p.S = 2 * c.sensor_range + 1;
+    p.ego = c.egoradius;
+    p.ow = 2 * c.egoradius + 1;
+    p.C = env->obs_C;
+    p.sensor = c.sensor_type;
+    p.n_lasers = c.num_lasers;
+    p.beams = env->beams_dev;
+    p.single_tool = c.single_square_tool;
+    p.comm_radius = c.comm_radius;
+    p.want_adj = 1;
+    p.dist_reward = c.dist_reward;
+    p.maxsteps = c.maxsteps;
+    p.truncate_steps = c.truncate_steps;
+    p.auto_reset = c.auto_reset;
+    p.env_id_base = c.env_id_base;
+    p.cp = c.collision_penalty;
+    p.terminal = c.terminal_reward;
+    p.done_incr = c.done_incr;
+    p.wall = env->wall;
+    p.pos = env->pos;
+    p.free_counts = env->free_counts;
+    p.n_maps = env->n_maps;
+    p.hdr = env->arena + l.off_hdr;
+    p.hdr_stride = l.hdr_stride;
+    p.off_pos = l.hdr_off_pos;
+    p.off_cov = l.hdr_off_cov;
+    p.off_adj = l.hdr_off_adj;
+    p.visited = reinterpret_cast<uint32_t*>(env->arena + l.off_visited);
+    p.fo = reinterpret_cast<uint2*>(env->arena + l.off_fo);
+    p.needs_reset = env->arena + l.off_needs_reset;
+    p.obs_env_floats = p.N * p.C * p.ow * p.ow;
+}
+
+void fill_super_params(mcov_env* env, mcov::SuperParams& p) {
+    const mcov_config& c = env->cfg;
+    const mcov_layout& l = env->lay;
+    memset(&p, 0, sizeof(p));
+    p.E = c.num_envs;
+    p.N = c.num_robots;
+    p.g = env->g;
+    p.R = c.senseradius;
+    p.C = env->obs_C;
+    p.use_scanning = c.use_scanning;
+    p.dist_reward = c.dist_reward;
+    p.truncate_steps = c.truncate_steps;
+    p.auto_reset = c.auto_reset;
+    p.env_id_base = c.env_id_base;
+    p.cp = c.collision_penalty;
+    p.terminal = c.terminal_reward;
+    p.done_incr = c.done_incr;
+    p.free_penalty = c.free_penalty;
+    p.wall = env->wall;
+    p.pos = env->pos;
+    p.free_counts = env->free_counts;
+    p.n_maps = env->n_maps;
+    p.hdr = env->arena + l.off_hdr;
+    p.hdr_stride = l.hdr_stride;
+    p.off_pos = l.hdr_off_pos;
+    p.off_cov = l.hdr_off_cov;
+    p.covered = reinterpret_cast<uint32_t*>(env->arena + l.off_covered);
+    p.seen_obst = reinterpret_cast<uint32_t*>(env->arena + l.off_seen_obst);
+    p.needs_reset = env->arena + l.off_needs_reset;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcov_abi_version(void) { return MCOV_ABI_VERSION; }
+
+const char* mcov_last_error(void) { return g_err; }
+
+int mcov_plane_geometry(int W, int L, int* strips_out, int* wp_out, int* words_out) {
+    if (W <= 0 || L <= 0) return fail(MCOV_ERR_BAD_CONFIG, "map size %d x %d", W, L);
+    const mcov::Geometry g = mcov::make_geometry(W, L);
+    if (strips_out) *strips_out = g.strips;
+    if (wp_out) *wp_out = g.Wp;
+    if (words_out) *words_out = g.PW;
+    return MCOV_OK;
+}
+
+int mcov_create(const mcov_config* cfg, mcov_env** out) {
+    if (!cfg || !out) return fail(MCOV_ERR_NULL, "cfg/out is NULL");
+    if (cfg->struct_size != (int32_t)sizeof(mcov_config))
+        return fail(MCOV_ERR_ABI, "mcov_config.struct_size %d != %d (ABI %d)", cfg->struct_size,
+                    (int)sizeof(mcov_config), MCOV_ABI_VERSION);
+    const mcov_config& c = *cfg;
+    if (c.env_type != MCOV_ENV_DEC && c.env_type != MCOV_ENV_SUPER)
+        return fail(MCOV_ERR_BAD_CONFIG, "env_type %d", c.env_type);
+    if (c.num_envs < 1) return fail(MCOV_ERR_BAD_CONFIG, "num_envs %d < 1", c.num_envs);
+    if (c.num_robots < 1 || c.num_robots > MCOV_MAX_ROBOTS)
+        return fail(MCOV_ERR_BAD_CONFIG, "numrobot %d outside [1, %d]", c.num_robots, MCOV_MAX_ROBOTS);
+    if (c.env_type == MCOV_ENV_DEC) {
+        if (c.sensor_type != MCOV_SENSOR_SQUARE && c.sensor_type != MCOV_SENSOR_LIDAR)
+            return fail(MCOV_ERR_BAD_CONFIG, "sensor_type %d", c.sensor_type);
+        if (c.sensor_range < 0 || c.sensor_range > MCOV_MAX_RADIUS)
+            return fail(MCOV_ERR_BAD_CONFIG, "sensor range %d outside [0, %d]", c.sensor_range, MCOV_MAX_RADIUS);
+        if (c.egoradius < 0 || c.egoradius > MCOV_MAX_RADIUS)
+            return fail(MCOV_ERR_BAD_CONFIG, "egoradius %d outside [0, %d]", c.egoradius, MCOV_MAX_RADIUS);
+        if (c.mini_map_rad < 0 || c.mini_map_rad > MCOV_MAX_RADIUS)
+            return fail(MCOV_ERR_BAD_CONFIG, "mini_map_rad %d outside [0, %d]", c.mini_map_rad, MCOV_MAX_RADIUS);
+        if (c.sensor_type == MCOV_SENSOR_LIDAR) {
+            if (c.num_lasers < 1 || c.num_lasers > MCOV_MAX_LASERS || (c.num_lasers % 2) == 0)
+                return fail(MCOV_ERR_BAD_CONFIG, "num_lasers %d must be odd and in [1, %d] (lidar.py:11)",
+                            c.num_lasers, MCOV_MAX_LASERS);
+        }
+        if (c.comm_radius < 0) return fail(MCOV_ERR_BAD_CONFIG, "comm_radius %d < 0", c.comm_radius);
+    } else {
+        if (c.senseradius < 0 || c.senseradius > MCOV_MAX_RADIUS)
+            return fail(MCOV_ERR_BAD_CONFIG, "senseradius %d outside [0, %d]", c.senseradius, MCOV_MAX_RADIUS);
+    }
+    mcov_env* e = new (std::nothrow) mcov_env();
+    if (!e) return fail(MCOV_ERR_CUDA, "out of host memory");
+    memset(e, 0, sizeof(*e));
+    e->cfg = c;
+    cudaError_t ce = cudaGetDevice(&e->device);
+    if (ce != cudaSuccess) { delete e; return cuda_fail(ce, "cudaGetDevice"); }
+    ce = cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, e->device);
+    if (ce != cudaSuccess) { delete e; return cuda_fail(ce, "cudaDeviceGetAttribute"); }
+    e->obs_C = obs_channels(c);
+    *out = e;
+    return MCOV_OK;
+}
+
+int mcov_destroy(mcov_env* env) {
+    if (!env) return MCOV_OK;
+    if (env->beams_dev) cudaFree(env->beams_dev);
+    delete env;
+    return MCOV_OK;
+}
+
+int mcov_set_lidar_beams(mcov_env* env, const double* beams_host, int num_lasers) {
+    if (!env || !beams_host) return fail(MCOV_ERR_NULL, "env/beams is NULL");
+    if (num_lasers != env->cfg.num_lasers)
+        return fail(MCOV_ERR_BAD_CONFIG, "num_lasers %d != config %d", num_lasers, env->cfg.num_lasers);
+    if (!env->beams_dev) {
+        cudaError_t ce = cudaMalloc(&env->beams_dev, sizeof(double) * 3 * num_lasers);
+        if (ce != cudaSuccess) return cuda_fail(ce, "cudaMalloc(beams)");
+    }
+    cudaError_t ce = cudaMemcpy(env->beams_dev, beams_host, sizeof(double) * 3 * num_lasers,
+                                cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaMemcpy(beams)");
+    return MCOV_OK;
+}
+
+int mcov_pack_maps(const int8_t* cells_dev, int n_maps, int W, int L, int add_border,
+                   uint32_t* wall_out_dev, uint32_t* pos_out_dev, int32_t* free_counts_out_dev,
+                   void* stream) {
+    if (!cells_dev || !wall_out_dev || !pos_out_dev || !free_counts_out_dev)
+        return fail(MCOV_ERR_NULL, "mcov_pack_maps: NULL buffer");
+    if (n_maps < 1 || W < 1 || L < 1) return fail(MCOV_ERR_BAD_CONFIG, "n_maps/W/L %d/%d/%d", n_maps, W, L);
+    const int b = add_border ? 1 : 0;
+    const mcov::Geometry g = mcov::make_geometry(W + 2 * b, L + 2 * b);
+    if (g.W > 32767 || g.L > 32767) return fail(MCOV_ERR_BAD_CONFIG, "map larger than int16 coordinates");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long total = (long long)n_maps * g.PW;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    pack_maps_kernel<<<grid, 256, 0, st>>>(cells_dev, n_maps, W, L, b, g.strips, g.Wp, wall_out_dev, pos_out_dev);
+    count_free_kernel<<<n_maps, 256, 0, st>>>(pos_out_dev, n_maps, g.PW, free_counts_out_dev);
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) return cuda_fail(ce, "pack_maps launch");
+    return MCOV_OK;
+}
+
+int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_dev,
+                  const int32_t* free_counts_dev, int n_maps, int W, int L) {
+    if (!env || !wall_dev || !pos_dev || !free_counts_dev) return fail(MCOV_ERR_NULL, "mcov_set_maps: NULL");
+    if (n_maps < 1 || W < 1 || L < 1 || W > 32767 || L > 32767)
+        return fail(MCOV_ERR_BAD_CONFIG, "n_maps/W/L %d/%d/%d", n_maps, W, L);
+    if (!aligned(wall_dev, 16) || !aligned(pos_dev, 16))
+        return fail(MCOV_ERR_ALIGN, "map planes must be 16-byte aligned");
+    env->g = mcov::make_geometry(W, L);
+    env->wall = wall_dev;
+    env->pos = pos_dev;
+    env->free_counts = free_counts_dev;
+    env->n_maps = n_maps;
+    env->maps_set = true;
+    env->bound = false;
+
+    // ---- arena layout ---------------------------------------------------------------------------
+    const mcov_config& c = env->cfg;
+    mcov_layout& l = env->lay;
+    memset(&l, 0, sizeof(l));
+    l.struct_size = (int32_t)sizeof(mcov_layout);
+    l.W = W; l.L = L;
+    l.strips = env->g.strips; l.Wp = env->g.Wp; l.plane_words = env->g.PW;
+    const int N = c.num_robots;
+    l.hdr_off_pos = (int32_t)sizeof(mcov::EnvHead);
+    l.hdr_off_cov = l.hdr_off_pos + 4 * N;
+    l.hdr_off_adj = l.hdr_off_cov + 4 * N;
+    l.hdr_stride = mcov::round_up(l.hdr_off_adj + 4 * N, 32);
+    const int64_t E = c.num_envs;
+    int64_t off = 0;
+    l.off_hdr = off; off = align_up64(off + E * l.hdr_stride, 256);
+    if (c.env_type == MCOV_ENV_DEC) {
+        l.off_visited = off; off = align_up64(off + E * (int64_t)l.plane_words * 4, 256);
+        l.off_fo = off; off = align_up64(off + E * N * (int64_t)l.plane_words * 8, 256);
+        l.off_covered = l.off_seen_obst = -1;
+    } else {
+        l.off_covered = off; off = align_up64(off + E * (int64_t)l.plane_words * 4, 256);
+        l.off_seen_obst = off; off = align_up64(off + E * (int64_t)l.plane_words * 4, 256);
+        l.off_visited = l.off_fo = -1;
+    }
+    l.off_needs_reset = off; off = align_up64(off + E, 256);
+    // scratch: stats partials (one row per CTA of the largest grid) + per-env float32 dist term
+    const int64_t max_grid = (int64_t)env->num_sms * 32;
+    l.off_scratch = off;
+    off = align_up64(off + max_grid * MCOV_STATS_LEN * 8, 256);
+    off = align_up64(off + E * 4, 256);
+    l.total_bytes = off;
+    return MCOV_OK;
+}
+
+int mcov_state_layout(const mcov_env* env, mcov_layout* out) {
+    if (!env || !out) return fail(MCOV_ERR_NULL, "env/out is NULL");
+    if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+    if (out->struct_size != 0 && out->struct_size != (int32_t)sizeof(mcov_layout))
+        return fail(MCOV_ERR_ABI, "mcov_layout.struct_size %d != %d", out->struct_size, (int)sizeof(mcov_layout));
+    *out = env->lay;
+    return MCOV_OK;
+}
+
+int mcov_bind_state(mcov_env* env, void* arena_dev, size_t bytes, void* stream) {
+    if (!env || !arena_dev) return fail(MCOV_ERR_NULL, "env/arena is NULL");
+    if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+    if (!aligned(arena_dev, 256)) return fail(MCOV_ERR_ALIGN, "state arena must be 256-byte aligned");
+    if ((int64_t)bytes < env->lay.total_bytes)
+        return fail(MCOV_ERR_BAD_CONFIG, "arena %zu bytes < required %lld", bytes, (long long)env->lay.total_bytes);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    env->arena = static_cast<unsigned char*>(arena_dev);
+    cudaError_t ce = cudaMemsetAsync(arena_dev, 0, (size_t)env->lay.total_bytes, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaMemsetAsync(arena)");
+    ce = mcov::launch_init_headers(env, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "init_headers launch");
+    env->bound = true;
+    return MCOV_OK;
+}
+
+int mcov_obs_shape(const mcov_env* env, int32_t dims_out[5], int32_t* ndims_out) {
+    if (!env || !dims_out || !ndims_out) return fail(MCOV_ERR_NULL, "NULL argument");
+    const mcov_config& c = env->cfg;
+    if (c.env_type == MCOV_ENV_DEC) {
+        dims_out[0] = c.num_envs; dims_out[1] = c.num_robots; dims_out[2] = env->obs_C;
+        dims_out[3] = dims_out[4] = 2 * c.egoradius + 1;
+        *ndims_out = 5;
+    } else {
+        if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+        dims_out[0] = c.num_envs; dims_out[1] = env->obs_C; dims_out[2] = env->g.W; dims_out[3] = env->g.L;
+        dims_out[4] = 0;
+        *ndims_out = 4;
+    }
+    return MCOV_OK;
+}
+
+static int run_dec(mcov_env* env, int mode, const void* actions, int act_fmt, const uint8_t* mask,
+                   int mask_from_flags, const int32_t* map_idx, const int16_t* start_xy, uint64_t seed,
+                   float* obs, float* reward, double* reward64, uint8_t* done, double* stats,
+                   cudaStream_t st) {
+    mcov::DecParams p;
+    fill_dec_params(env, p);
+    p.mode = mode;
+    p.actions = actions;
+    p.act_fmt = act_fmt;
+    p.mask = mask;
+    p.mask_from_flags = mask_from_flags;
+    p.map_idx_in = map_idx;
+    p.start_xy_in = start_xy;
+    p.seed = seed;
+    p.obs = obs;
+    p.reward = reward;
+    p.reward64 = reward64;
+    p.done = done;
+    p.bulk_ok = ((p.obs_env_floats * 4) % 16 == 0) && aligned(obs, 16);
+    double* partial = reinterpret_cast<double*>(env->arena + env->lay.off_scratch);
+    p.stats_partial = (stats && mode == mcov::MODE_STEP) ? partial : nullptr;
+    const mcov_config& c = env->cfg;
+    const bool extras = c.dist_reward || c.dijkstra_input || c.mini_map_rad > 0;
+    cudaError_t ce;
+    if (mode == mcov::MODE_STEP && c.map_sharing) {
+        ce = mcov::launch_dec_share(env, st);                     // dec_grid_rl.py:124-125
+        if (ce != cudaSuccess) return cuda_fail(ce, "dec_share launch");
+    }
+    if (c.dist_reward && mode == mcov::MODE_STEP) {
+        // distance term uses the PRE-sensing memory at the POST-move pose: needs the moves first.
+        // handled inside launch_dec_extras(pre_sense=1) which replays the move resolution.
+        p.dist_term = reinterpret_cast<float*>(env->arena + env->lay.off_scratch +
+                                               align_up64((int64_t)env->num_sms * 32 * MCOV_STATS_LEN * 8, 256));
+        ce = mcov::launch_dec_extras(env, nullptr, 1, st);
+        if (ce != cudaSuccess) return cuda_fail(ce, "dec dist-term launch");
+    }
+    ce = mcov::launch_dec(env, p, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "dec kernel launch");
+    if (extras) {
+        ce = mcov::launch_dec_extras(env, obs, 0, st);
+        if (ce != cudaSuccess) return cuda_fail(ce, "dec extras launch");
+    }
+    if (p.stats_partial) {
+        ce = mcov::launch_stats_reduce(env, partial, mcov::dec_grid_size(env), stats, st);
+        if (ce != cudaSuccess) return cuda_fail(ce, "stats reduce launch");
+    }
+    return MCOV_OK;
+}
+
+static int run_super(mcov_env* env, int mode, const void* actions, int act_fmt, const uint8_t* mask,
+                     int mask_from_flags, const int32_t* map_idx, const int16_t* start_xy,
+                     uint64_t seed, float* obs, float* reward, double* reward64, uint8_t* done,
+                     double* stats, cudaStream_t st) {
+    mcov::SuperParams p;
+    fill_super_params(env, p);
+    p.mode = mode;
+    p.actions = actions;
+    p.act_fmt = act_fmt;
+    p.mask = mask;
+    p.mask_from_flags = mask_from_flags;
+    p.map_idx_in = map_idx;
+    p.start_xy_in = start_xy;
+    p.seed = seed;
+    p.obs = obs;
+    p.reward = reward;
+    p.reward64 = reward64;
+    p.done = done;
+    double* partial = reinterpret_cast<double*>(env->arena + env->lay.off_scratch);
+    p.stats_partial = (stats && mode == mcov::MODE_STEP) ? partial : nullptr;
+    cudaError_t ce = mcov::launch_super(env, p, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "super kernel launch");
+    if (p.stats_partial) {
+        ce = mcov::launch_stats_reduce(env, partial, mcov::super_grid_size(env), stats, st);
+        if (ce != cudaSuccess) return cuda_fail(ce, "stats reduce launch");
+    }
+    return MCOV_OK;
+}
+
+int mcov_reset(mcov_env* env, const uint8_t* mask_dev, const int32_t* map_idx_dev,
+               const int16_t* start_xy_dev, uint64_t seed, float* obs_out_dev, void* stream) {
+    int rc = check_ready(env);
+    if (rc) return rc;
+    if (!obs_out_dev) return fail(MCOV_ERR_NULL, "obs_out is NULL");
+    if (!aligned(obs_out_dev, 16)) return fail(MCOV_ERR_ALIGN, "obs_out must be 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (env->cfg.env_type == MCOV_ENV_DEC)
+        return run_dec(env, mcov::MODE_RESET, nullptr, 0, mask_dev, 0, map_idx_dev, start_xy_dev, seed,
+                       obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
+    return run_super(env, mcov::MODE_RESET, nullptr, 0, mask_dev, 0, map_idx_dev, start_xy_dev, seed,
+                     obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
+}
+
+int mcov_step(mcov_env* env, const void* actions_dev, int action_format, float* obs_out_dev,
+              float* reward_out_dev, double* reward64_out_dev, uint8_t* done_out_dev,
+              double* stats_out_dev, void* stream) {
+    int rc = check_ready(env);
+    if (rc) return rc;
+    if (!actions_dev || !obs_out_dev || !reward_out_dev || !done_out_dev)
+        return fail(MCOV_ERR_NULL, "mcov_step: actions/obs/reward/done is NULL");
+    if (action_format != MCOV_ACT_U8_PER_ROBOT && action_format != MCOV_ACT_I64_BASE4)
+        return fail(MCOV_ERR_BAD_CONFIG, "action_format %d", action_format);
+    if (action_format == MCOV_ACT_I64_BASE4 && env->cfg.num_robots > 31)
+        return fail(MCOV_ERR_BAD_CONFIG, "base-4 int64 actions hold at most 31 robots");
+    if (action_format == MCOV_ACT_I64_BASE4 && !aligned(actions_dev, 8))
+        return fail(MCOV_ERR_ALIGN, "int64 actions must be 8-byte aligned");
+    if (!aligned(obs_out_dev, 16)) return fail(MCOV_ERR_ALIGN, "obs_out must be 16-byte aligned");
+    if (!aligned(reward_out_dev, 4) || (reward64_out_dev && !aligned(reward64_out_dev, 8)))
+        return fail(MCOV_ERR_ALIGN, "reward buffers misaligned");
+    if (stats_out_dev && !aligned(stats_out_dev, 8)) return fail(MCOV_ERR_ALIGN, "stats_out misaligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool dec = env->cfg.env_type == MCOV_ENV_DEC;
+    rc = dec ? run_dec(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, 0,
+                       obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st)
+             : run_super(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, 0,
+                         obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
+    if (rc) return rc;
+    if (env->cfg.auto_reset) {
+        // finished / truncated envs restart in place; their obs rows become the new episode's first
+        // observation (gym auto-reset convention).  Seed: config-independent constant mixed with the
+        // per-slot episode counter inside the kernel.
+        const uint64_t seed = 0x9E3779B97F4A7C15ull ^ (uint64_t)env->cfg.env_id_base;
+        rc = dec ? run_dec(env, mcov::MODE_RESET, nullptr, 0, nullptr, 1, nullptr, nullptr, seed,
+                           obs_out_dev, nullptr, nullptr, nullptr, nullptr, st)
+                 : run_super(env, mcov::MODE_RESET, nullptr, 0, nullptr, 1, nullptr, nullptr, seed,
+                             obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
+    }
+    return rc;
+}
+
+int mcov_observe(mcov_env* env, float* obs_out_dev, void* stream) {
+    int rc = check_ready(env);
+    if (rc) return rc;
+    if (!obs_out_dev) return fail(MCOV_ERR_NULL, "obs_out is NULL");
+    if (!aligned(obs_out_dev, 16)) return fail(MCOV_ERR_ALIGN, "obs_out must be 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (env->cfg.env_type == MCOV_ENV_DEC)
+        return run_dec(env, mcov::MODE_OBSERVE, nullptr, 0, nullptr, 0, nullptr, nullptr, 0, obs_out_dev,
+                       nullptr, nullptr, nullptr, nullptr, st);
+    return run_super(env, mcov::MODE_OBSERVE, nullptr, 0, nullptr, 0, nullptr, nullptr, 0, obs_out_dev,
+                     nullptr, nullptr, nullptr, nullptr, st);
+}
+
+int mcov_percent_covered(mcov_env* env, double* out_dev, void* stream) {
+    int rc = check_ready(env);
+    if (rc) return rc;
+    if (!out_dev) return fail(MCOV_ERR_NULL, "out is NULL");
+    cudaError_t ce = mcov::launch_percent_covered(env, out_dev, static_cast<cudaStream_t>(stream));
+    if (ce != cudaSuccess) return cuda_fail(ce, "percent_covered launch");
+    return MCOV_OK;
+}
+
+int64_t mcov_launch_count(const mcov_env* env) { return env ? env->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,120 @@
+// mcov_internal.h — host-side handle and kernel parameter blocks (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/mcov.h"
+#include "mcov_common.cuh"
+
+namespace mcov {
+
+enum { MODE_STEP = 0, MODE_RESET = 1, MODE_OBSERVE = 2 };
+
+// Parameter block of the DecGridRL kernels (passed by value).
+struct DecParams {
+    int E, N;
+    Geometry g;
+    int R, S;                 // sensor range, S = 2R+1 rows/bits of the sensor window
+    int ego, ow;              // egoradius, ow = 2*ego+1
+    int C;                    // observation channels (3 + extras)
+    int sensor;               // MCOV_SENSOR_*
+    int n_lasers;
+    const double* beams;      // [n_lasers][3] device
+    int single_tool, comm_radius, want_adj, dist_reward;
+    int maxsteps, truncate_steps, auto_reset;
+    int env_id_base;
+    double cp, terminal, done_incr;
+    // maps
+    const uint32_t* wall;
+    const uint32_t* pos;
+    const int32_t* free_counts;
+    int n_maps;
+    // state
+    unsigned char* hdr;
+    int hdr_stride, off_pos, off_cov, off_adj;
+    uint32_t* visited;
+    uint2* fo;
+    uint8_t* needs_reset;
+    float* dist_term;         // [E] float32 distance-reward term prepared by the dist kernel (or null)
+    // io
+    int mode;
+    const void* actions;
+    int act_fmt;
+    const uint8_t* mask;      // reset: which envs (null = all); MODE_RESET with from_flags uses needs_reset
+    int mask_from_flags;
+    const int32_t* map_idx_in;
+    const int16_t* start_xy_in;
+    uint64_t seed;
+    float* obs;
+    float* reward;
+    double* reward64;
+    uint8_t* done;
+    double* stats_partial;    // [gridDim][MCOV_STATS_LEN] or null
+    int obs_env_floats;       // N*C*ow*ow
+    int bulk_ok;              // env obs block is a multiple of 16 bytes and obs is 16B aligned
+};
+
+struct SuperParams {
+    int E, N;
+    Geometry g;
+    int R;                    // senseradius
+    int C;                    // N+3, or 4 with use_scanning
+    int use_scanning, dist_reward;
+    int truncate_steps, auto_reset, env_id_base;
+    double cp, terminal, done_incr, free_penalty;
+    const uint32_t* wall;
+    const uint32_t* pos;
+    const int32_t* free_counts;
+    int n_maps;
+    unsigned char* hdr;
+    int hdr_stride, off_pos, off_cov;
+    uint32_t* covered;
+    uint32_t* seen_obst;
+    uint8_t* needs_reset;
+    int mode;
+    const void* actions;
+    int act_fmt;
+    const uint8_t* mask;
+    int mask_from_flags;
+    const int32_t* map_idx_in;
+    const int16_t* start_xy_in;
+    uint64_t seed;
+    float* obs;
+    float* reward;
+    double* reward64;
+    uint8_t* done;
+    double* stats_partial;
+};
+
+}  // namespace mcov
+
+struct mcov_env {
+    mcov_config cfg;
+    int device;
+    int num_sms;
+    bool maps_set, bound;
+    mcov::Geometry g;
+    const uint32_t* wall;
+    const uint32_t* pos;
+    const int32_t* free_counts;
+    int n_maps;
+    mcov_layout lay;
+    unsigned char* arena;
+    double* beams_dev;        // owned
+    int64_t launches;
+    int obs_C;
+};
+
+// kernel launchers (defined in the .cu files)
+namespace mcov {
+cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st);
+cudaError_t launch_dec_share(mcov_env* env, cudaStream_t st);
+cudaError_t launch_dec_extras(mcov_env* env, float* obs, int pre_sense, cudaStream_t st);
+cudaError_t launch_super(mcov_env* env, SuperParams& p, cudaStream_t st);
+cudaError_t launch_stats_reduce(mcov_env* env, const double* partial, int rows, double* out,
+                                cudaStream_t st);
+cudaError_t launch_init_headers(mcov_env* env, cudaStream_t st);
+cudaError_t launch_percent_covered(mcov_env* env, double* out, cudaStream_t st);
+int dec_grid_size(const mcov_env* env);
+int super_grid_size(const mcov_env* env);
+}  // namespace mcov

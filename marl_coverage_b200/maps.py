@@ -1,0 +1,133 @@
+"""Map supply for the batched env: the reference's ``gridload`` / ``gridgen`` contract
+(Utils/gridmaker.py:7-139) plus the device-side bit packer.
+
+A "grid" is what the reference hands to the env ctor: a float array [W, L] with <0 obstacle,
+>0 free (PNG maps: exactly -1 / +1), axis 0 = x.  ``MapTable`` packs a list of grids into the
+strip-major bit planes of include/mcov.h with the CUDA packer ``mcov_pack_maps``.
+"""
+import os
+
+import numpy as np
+
+from . import _lib
+
+DATA_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data", "grids")
+
+
+def load_grid_set(name, limit=None):
+    """Committed copy of the reference's Grids/<name> PNG set, SORTED by filename, as the float64
+    +-1 grids ``gridload`` produces (gridmaker.py:89-92)."""
+    z = np.load(os.path.join(DATA_DIR, name + ".npz"))
+    W, L = (int(v) for v in z["shape"])
+    bits = z["bits"] if limit is None else z["bits"][:limit]
+    out = []
+    for row in bits:
+        free = np.unpackbits(row)[:W * L].reshape(W, L)
+        out.append(np.where(free > 0, 1.0, -1.0))
+    return out
+
+
+def gridload(grid_config=None):
+    """Same contract as Utils/gridmaker.py:7-104: returns (train_set, test_set).
+
+    ``grid_config=None`` -> the nine hand-made 15x15 maps (6 train / 3 test).  Otherwise
+    ``grid_dir`` may be a directory of PNGs (read like the reference, but in SORTED order so runs
+    are reproducible — the reference uses raw os.listdir order) or the name of a committed set."""
+    if grid_config is None:
+        z = np.load(os.path.join(DATA_DIR, "builtin15.npz"))
+        grids = load_grid_set("builtin15")
+        n_train = int(z["n_train"])
+        return grids[:n_train], grids[n_train:]
+    grid_dir = grid_config["grid_dir"]
+    numgrids = grid_config["numgrids"]
+    base = os.path.basename(os.path.normpath(grid_dir))
+    if os.path.isdir(grid_dir):
+        from PIL import Image
+        gridlis = []
+        for fname in sorted(os.listdir(grid_dir))[:numgrids]:
+            img = np.array(Image.open(os.path.join(grid_dir, fname))).astype(float)
+            gridlis.append(np.clip(img - 1, -1, 1))
+    elif os.path.exists(os.path.join(DATA_DIR, base + ".npz")):
+        gridlis = load_grid_set(base, numgrids)
+    else:
+        raise FileNotFoundError(grid_dir)
+    half = len(gridlis) // 2
+    if half == 1:
+        return gridlis, gridlis
+    return gridlis[:half], gridlis[half:]
+
+
+def gridgen(grid_config):
+    """Bernoulli obstacle maps — Utils/gridmaker.py:107-139 (same np.random call, same split)."""
+    p = grid_config["prob_obst"]
+    gridlis = [np.random.choice(a=[1.0, -1.0], size=(grid_config["gridwidth"], grid_config["gridlen"]),
+                                p=[1 - p, p]) for _ in range(grid_config["numgrids"])]
+    n = len(gridlis)
+    if n == 1:
+        return gridlis, gridlis
+    return gridlis[:n], gridlis[n:]
+
+
+def grids_to_cells(grids):
+    """float grids -> int8 sign cells [M, W, L]; rejects maps the bit planes cannot represent."""
+    arr = np.stack([np.asarray(g, dtype=np.float64) for g in grids])
+    cells = np.sign(arr).astype(np.int8)
+    if not np.array_equal(np.where(arr > 0, 1.0, np.where(arr < 0, -1.0, 0.0)), arr):
+        raise ValueError("maps must hold only -1 / 0 / +1 cells (PNG maps do); per-cell reward "
+                         "values other than 1 are outside this build's scope")
+    return cells
+
+
+# ---- host-side (numpy) view of the strip-major layout: used by tests and get_state --------------
+
+def pack_plane_host(mask):
+    """bool [W, L] -> uint32 [strips * Wp] strip-major words (include/mcov.h)."""
+    W, L = mask.shape
+    strips, Wp, PW = _geometry(W, L)
+    out = np.zeros((strips, Wp), dtype=np.uint32)
+    pad = np.zeros((W, strips * 32), dtype=np.uint64)
+    pad[:, :L] = mask
+    weights = (np.uint64(1) << np.arange(32, dtype=np.uint64))
+    for s in range(strips):
+        out[s, :W] = (pad[:, 32 * s:32 * s + 32] * weights).sum(axis=1).astype(np.uint32)
+    return out.reshape(-1)
+
+
+def unpack_plane_host(words, W, L):
+    """uint32 [..., strips * Wp] -> bool [..., W, L]."""
+    strips, Wp, PW = _geometry(W, L)
+    w = np.asarray(words, dtype=np.uint32).reshape(words.shape[:-1] + (strips, Wp))
+    bits = (w[..., None] >> np.arange(32, dtype=np.uint32)) & np.uint32(1)       # [..., s, x, 32]
+    bits = np.moveaxis(bits, -3, -2)                                              # [..., x, s, 32]
+    bits = bits.reshape(bits.shape[:-2] + (strips * 32,))
+    return bits[..., :W, :L].astype(bool)
+
+
+def _geometry(W, L):
+    strips = (L + 31) // 32
+    Wp = (W + 3) // 4 * 4
+    return strips, Wp, strips * Wp
+
+
+class MapTable:
+    """Device table of packed maps: ``wall`` / ``pos`` uint32 [M, plane_words] and ``free_counts``
+    int32 [M] (= np.count_nonzero(grid > 0), dec_grid_rl.py:517), built by the CUDA packer."""
+
+    def __init__(self, grids, add_border, device):
+        import torch
+        lib = _lib.load()
+        cells = grids_to_cells(grids)
+        M, W, L = cells.shape
+        b = 1 if add_border else 0
+        self.n_maps, self.W, self.L = M, W + 2 * b, L + 2 * b
+        self.strips, self.Wp, self.plane_words = _lib.plane_geometry(self.W, self.L)
+        self.device = torch.device(device)
+        with torch.cuda.device(self.device):
+            cells_dev = torch.from_numpy(cells).to(self.device)
+            self.wall = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
+            self.pos = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
+            self.free_counts = torch.empty((M,), dtype=torch.int32, device=self.device)
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            _lib.check(lib.mcov_pack_maps(cells_dev.data_ptr(), M, W, L, b, self.wall.data_ptr(),
+                                          self.pos.data_ptr(), self.free_counts.data_ptr(), st))
+            torch.cuda.current_stream(self.device).synchronize()   # cells_dev may be freed now

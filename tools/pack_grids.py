@@ -37,6 +37,19 @@ def main():
         np.savez_compressed(p, names=np.array(files), shape=np.array(shape, dtype=np.int32),
                             bits=np.stack(bits))
         print(name, len(files), shape, "%.1f kB" % (os.path.getsize(p) / 1e3))
+    # the nine 15x15 maps gridload(None) builds in code (Utils/gridmaker.py:24-80): 6 train + 3 test
+    sys.path.insert(0, rh.REFERENCE_ROOT)
+    rh._install_stubs()
+    from Utils.gridmaker import gridload
+    with rh.quiet():
+        train, test = gridload(None)
+    grids = train + test
+    names = ["train%d" % (k + 1) for k in range(len(train))] + ["test%d" % (k + 1) for k in range(len(test))]
+    p = os.path.join(out, "builtin15.npz")
+    np.savez_compressed(p, names=np.array(names), shape=np.array(grids[0].shape, dtype=np.int32),
+                        bits=np.stack([np.packbits((g > 0).ravel()) for g in grids]),
+                        n_train=np.int32(len(train)))
+    print("builtin15", len(grids), grids[0].shape, "%.1f kB" % (os.path.getsize(p) / 1e3))
 
 
 if __name__ == "__main__":
