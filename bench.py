@@ -1,0 +1,522 @@
+#!/usr/bin/env python
+"""bench.py — agent-steps/s of the batched MARL-Coverage env step on B200 (contract: task brief).
+
+One "step" = one pass of the hot path (DecGridRL.step for every env of this GPU's shard, with
+auto-reset and episode statistics) over one batch of synthetic actions.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c2|c3|c4|super] [--impl reference]
+
+Default workload "c5" = BASELINE.json configs[4]: weak scaling, 131 072 envs per GPU x 4 agents on
+bg2_100x100, per-env settings of configs[1] (square sensor range 2, egoradius 5, obs [4,3,11,11] f32).
+State + observations are ~2.9 GB per GPU, far larger than the 126 MB L2, so no L2 flush is needed.
+The JSON line also carries `c2_4096` = configs[1] at its literal size (4096 envs, L2 flushed between
+timed steps).
+
+`--impl reference` times the CPU implementation of the same path (the numpy oracle port of the
+pure-Python reference — the reference itself cannot travel to the GPU box) on all host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "agent-steps/sec (batched env step, 1/2/4/8 B200) and % of HBM roofline"
+UNIT = "agent-steps/s"
+
+DEC_BASE = dict(maxsteps=1000, collision_penalty=5, done_thresh=1, done_incr=0, terminal_reward=30,
+                dist_reward=0, train_maxsteps=1000, test_maxsteps=1000, egoradius=5, mini_map_rad=0,
+                comm_radius=0, allow_comm=0, map_sharing=0, single_square_tool=0, dijkstra_input=0)
+
+WORKLOADS = {
+    # name: (env kind, grid set, envs per GPU, env_config, description)
+    "c5": ("dec", "bg2_100x100", 131072,
+           dict(DEC_BASE, numrobot=4, sensor_type="square_sensor", sensor_config={"range": 2}),
+           "configs[4] weak scaling: 131072 envs/GPU x 4 agents, DecGridRL bg2_100x100, square sensor "
+           "r=2, egoradius 5 (per-env settings of configs[1])"),
+    "c2": ("dec", "bg2_100x100", 4096,
+           dict(DEC_BASE, numrobot=4, sensor_type="square_sensor", sensor_config={"range": 2}),
+           "configs[1]: 4096 envs x 4 agents, DecGridRL bg2_100x100, square sensor r=2, egoradius 5"),
+    "c3": ("dec", "bg2_256x256", 16384,
+           dict(DEC_BASE, numrobot=8, sensor_type="lidar", sensor_config={"range": 10, "num_lasers": 21}),
+           "configs[2]: 16384 envs x 8 agents, DecGridRL bg2_256x256, lidar 21 lasers range 10"),
+    "c4": ("dec", "bg2_1073x1073", 256,
+           dict(DEC_BASE, numrobot=16, sensor_type="square_sensor", sensor_config={"range": 2}),
+           "configs[3]: 256 envs x 16 agents, DecGridRL bg2_1073x1073, square sensor r=2"),
+    "super": ("super", "bg2_100x100", 8192,
+              dict(numrobot=4, train_maxsteps=1000, test_maxsteps=1000, collision_penalty=5,
+                   senseradius=2, free_penalty=0.2, done_thresh=1, done_incr=0, terminal_reward=30,
+                   dist_reward=0, use_scanning=0),
+              "C1 settings batched: 8192 envs x 4 agents, SuperGridRL bg2_100x100, senseradius 2, "
+              "full [7,100,100] f32 state"),
+}
+
+
+def alg_bytes_per_env_step(kind, cfg, W, L):
+    """SURVEY.md §8(d) algorithmic bytes per env-step (the roofline numerator)."""
+    N = cfg["numrobot"]
+    if kind == "super":
+        return (N + 3) * W * L * 4 + N * 1 + 5 + N * 8
+    e = cfg["egoradius"]
+    ow = 2 * e + 1
+    C = 3
+    R = cfg["sensor_config"]["range"]
+    S = 2 * R + 1
+    b_obs = N * C * ow * ow * 4
+    per_robot_rows = 3 * ow + 2 * S + S + 2 * S
+    if cfg["sensor_type"] == "lidar":
+        per_robot_rows += 2 * S
+    b_state = N * 8 * per_robot_rows + N * 16
+    return b_obs + N * 1 + 5 + N * 8 + b_state
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            with open(p) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(prefix="mcov_clocks_", suffix=".csv")
+            os.close(fd)
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:
+            pass
+        try:
+            self.f.close()
+            rows = [r.strip().split(",") for r in open(self.path) if r.strip()]
+            os.unlink(self.path)
+        except Exception:
+            return out
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if r[5 + k].strip().lower().startswith("active"):
+                    reasons.add(nm)
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------- CPU (oracle) arm
+def _cpu_worker(args):
+    kind, grid_name, cfg, seconds, warm, seed = args
+    import contextlib
+    import io
+    import numpy as np
+    from marl_coverage_b200.maps import load_grid_set
+    from oracle import coverage_oracle as oc
+    grids = load_grid_set(grid_name)
+    train = grids[:len(grids) // 2]
+    np.random.seed(seed)
+    rng = np.random.default_rng(seed)
+    N = cfg["numrobot"]
+    maxsteps = cfg["train_maxsteps"]
+    with contextlib.redirect_stdout(io.StringIO()):
+        env = oc.OracleDecGridRL(train, cfg) if kind == "dec" else oc.OracleSuperGridRL(train, cfg)
+        steps = 0
+        t_end_warm = time.perf_counter() + warm
+        t0 = None
+        while True:
+            a = int(rng.integers(0, 4 ** N)) if N <= 31 else rng.integers(0, 4, size=N)
+            _, _, done = env.step(a)
+            if done or env._currstep >= maxsteps:
+                env.reset(False, None)
+            now = time.perf_counter()
+            if t0 is None:
+                if now >= t_end_warm:
+                    t0 = now
+                continue
+            steps += 1
+            if now - t0 >= seconds:
+                return steps, now - t0
+
+
+def cpu_arm(kind, grid_name, cfg, seconds, warm, procs=None):
+    """Oracle port of the reference env on `procs` processes (one env object each, random base-4
+    actions, reset on done / train_maxsteps — BASELINE.md §3).  Returns (agent-steps/s, procs)."""
+    import multiprocessing as mp
+    procs = procs or len(os.sched_getaffinity(0))
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(procs) as pool:
+        res = pool.map(_cpu_worker, [(kind, grid_name, cfg, seconds, warm, 1000 + i) for i in range(procs)])
+    rate = sum(s / t for s, t in res) * cfg["numrobot"]
+    return rate, procs
+
+
+def run_reference(args):
+    kind, grid_name, E, cfg, desc = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    # each "step" of this arm is a bounded sample: `sample_s` seconds of stepping on every core
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    sample_s = min(5.0, max(1.0, 120.0 / (steps + warm)))
+    for _ in range(min(warm, 1)):
+        cpu_arm(kind, grid_name, cfg, 1.0, 0.5)
+    rates = []
+    t0 = time.perf_counter()
+    procs = None
+    for _ in range(min(steps, 6)):
+        r, procs = cpu_arm(kind, grid_name, cfg, sample_s, 0.5)
+        rates.append(r)
+        if time.perf_counter() - t0 > 150:
+            break
+    value = sum(rates) / len(rates)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "note": "CPU arm: numpy oracle port of the pure-Python reference env "
+                   "(the reference needs /root/reference, absent on the GPU box); one env per process, "
+                   "random base-4 actions, reset on done / train_maxsteps"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port",
+                         "sample": "%d x %.1f s of stepping on %d processes" % (len(rates), sample_s, procs)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------- GPU arm
+def make_env(kind, grid_name, cfg, E, device, env_id_base):
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, load_grid_set
+    grids = load_grid_set(grid_name)
+    train = grids[:len(grids) // 2]                       # gridload half split (gridmaker.py:96-102)
+    cls = VecDecGridRL if kind == "dec" else VecSuperGridRL
+    env = cls(train, cfg, num_envs=E, device=device, auto_reset=True,
+              truncate_steps=cfg["train_maxsteps"], env_id_base=env_id_base, seed=0)
+    return env, len(train)
+
+
+def gen_actions(torch, device, T, E, N, seed):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    return torch.randint(0, 4, (T, E, N), dtype=torch.uint8, device=device, generator=g)
+
+
+def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, flush=None):
+    """W untimed + K timed steps.  Returns (ms total over K by CUDA events, per-step ms list or None).
+    With `flush` (a big tensor) the L2 is overwritten between steps and each step is timed alone."""
+    dev = env.device
+    side = torch.cuda.Stream(device=dev) if world > 1 else None
+    ev_stats = [torch.cuda.Event() for _ in range(2)]
+    ev_red = [torch.cuda.Event() for _ in range(2)]
+    stats_bufs = [torch.zeros(8, dtype=torch.float64, device=dev) for _ in range(2)]
+    total_stats = torch.zeros(8, dtype=torch.float64, device=dev)
+    main = torch.cuda.current_stream(dev)
+
+    def one(k):
+        b = k & 1
+        if side is not None and k >= 2:
+            main.wait_event(ev_red[b])                   # all-reduce of step k-2 has left this buffer
+        env.stats = stats_bufs[b]
+        env.step(acts[k % acts.shape[0]], want_stats=True)
+        if side is not None:
+            ev_stats[b].record(main)
+            with torch.cuda.stream(side):
+                side.wait_event(ev_stats[b])
+                dist.all_reduce(stats_bufs[b])           # NCCL SUM of the 64-byte statistics vector
+                total_stats.add_(stats_bufs[b])
+                ev_red[b].record(side)
+        else:
+            total_stats.add_(stats_bufs[b])
+
+    for k in range(warmup):
+        one(k)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+    per = None
+    if flush is None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(main)
+        for k in range(warmup, warmup + steps):
+            one(k)
+        if side is not None:
+            main.wait_stream(side)
+        e1.record(main)
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1)
+    else:
+        per = []
+        evs = []
+        for k in range(warmup, warmup + steps):
+            flush.add_(1)                                # > L2-sized read+write
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(main)
+            one(k)
+            b.record(main)
+            evs.append((a, b))
+        torch.cuda.synchronize(dev)
+        per = [a.elapsed_time(b) for a, b in evs]
+        ms = sum(per)
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+    return ms, per, total_stats
+
+
+def run_gpu(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device; there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    import __graft_entry__ as ge
+    if rank == 0:
+        ge.build()
+    if world > 1:
+        dist.barrier()
+
+    kind, grid_name, E, cfg, desc = WORKLOADS[args.workload]
+    if args.envs_per_gpu:
+        E = args.envs_per_gpu
+    N = cfg["numrobot"]
+    K, Wm = args.steps, max(3, args.warmup)
+
+    env, n_maps = make_env(kind, grid_name, cfg, E, device, env_id_base=rank * E)
+    T = min(K + Wm, 64)
+    acts = gen_actions(torch, device, T, E, N, 1234 + rank)
+    map_idx = (torch.arange(E, device=device, dtype=torch.int32) + rank * E) % n_maps
+    env.reset(map_idx=map_idx)                           # start poses: device Philox, seed 0
+    torch.cuda.synchronize(device)
+
+    ws_bytes = env._arena.numel() + env.obs.numel() * 4
+    l2_bytes = 126 * 1024 * 1024
+    flush = None
+    if ws_bytes < 2 * l2_bytes:
+        flush = torch.zeros(256 * 1024 * 1024 // 4, dtype=torch.int32, device=device)
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    launches0 = env.launch_count
+    ms, per, total_stats = timed_steps(torch, dist, env, acts, Wm, K, world, flush=flush)
+    launches = env.launch_count - launches0
+    launches_timed = int(round(launches * K / float(K + Wm)))
+    clk = clocks.stop() if rank == 0 else None
+
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * E * N * K / (ms_max * 1e-3)
+
+    # ---- dominant kernel alone: the fused step kernel, one launch per call (no auto-reset kernel,
+    # no statistics reduction), timed per launch with CUDA events on the launching stream ----------
+    roof = None
+    e2e = None
+    c2_extra = None
+    cpu = None
+    if rank == 0 or world > 1:
+        pass
+    # kernel-only pass (every rank runs it so ranks stay in lock step; rank 0 reports)
+    envk, _ = make_env_kernel_only(kind, grid_name, cfg, E, device, rank)
+    envk.reset(map_idx=map_idx)
+    for k in range(Wm):
+        envk.step(acts[k % T])
+    torch.cuda.synchronize(device)
+    main = torch.cuda.current_stream(device)
+    evs = []
+    l0 = envk.launch_count
+    for k in range(min(K, 200)):
+        if flush is not None:
+            flush.add_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(main)
+        envk.step(acts[(Wm + k) % T])
+        b.record(main)
+        evs.append((a, b))
+    torch.cuda.synchronize(device)
+    kl = envk.launch_count - l0
+    kms = [a.elapsed_time(b) for a, b in evs]
+    k_avg_ms = sum(kms) / len(kms)
+    peak, peak_src = measured_peak()
+    balg = alg_bytes_per_env_step(kind, cfg, env.W, env.L)
+    achieved = balg * E / (k_avg_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": "dec_env_kernel" if kind == "dec" else "super_env_kernel",
+            "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": load_traffic(args.workload),
+            "alg_bytes_per_agent_step": balg / N, "kernel_ms": k_avg_ms, "launches_per_call": kl / len(kms),
+            "peak_source": peak_src}
+    del envk
+
+    # ---- e2e: host buffers through the public API: pinned host actions -> H2D, step,
+    # reward/done/stats -> D2H, synchronised every step (the caller reads them) -------------------
+    acts_host = acts.cpu().pin_memory()
+    act_dev = torch.empty((E, N), dtype=torch.uint8, device=device)
+    rew_host = torch.empty((E,), dtype=torch.float32).pin_memory()
+    done_host = torch.empty((E,), dtype=torch.uint8).pin_memory()
+    stats_host = torch.empty((8,), dtype=torch.float64).pin_memory()
+    Ke = min(K, 200)
+    for k in range(3):
+        act_dev.copy_(acts_host[k % T], non_blocking=True)
+        env.step(act_dev, want_stats=True)
+    torch.cuda.synchronize(device)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(main)
+    for k in range(Ke):
+        act_dev.copy_(acts_host[k % T], non_blocking=True)
+        _, r, d = env.step(act_dev, want_stats=True)
+        rew_host.copy_(r, non_blocking=True)
+        done_host.copy_(d, non_blocking=True)
+        stats_host.copy_(env.stats, non_blocking=True)
+        main.synchronize()
+    e1.record(main)
+    torch.cuda.synchronize(device)
+    te = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e = {"value": world * E * N * Ke / (float(te.item()) * 1e-3), "unit": UNIT,
+           "h2d_bytes_per_step": E * N, "d2h_bytes_per_step": E * 4 + E + 64,
+           "note": "observations stay in HBM for the policy; actions H2D, reward/done/stats D2H, "
+                   "host sync every step"}
+
+    if rank == 0 and world == 1 and args.workload == "c5" and not args.no_extras:
+        c2_extra = run_c2_extra(torch, device)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        rate, procs = cpu_arm(kind, grid_name, cfg, args.cpu_seconds, 1.0)
+        cpu = {"value": rate, "unit": UNIT, "cores": procs, "kind": "port",
+               "sample": "numpy oracle port of the reference env, %d processes x %.0f s of stepping "
+                         "(one env each, random base-4 actions, reset on done/train_maxsteps)"
+                         % (procs, args.cpu_seconds)}
+
+    if rank == 0:
+        st = total_stats.cpu().numpy()
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32 bit-planes (obs f32, reward f64)", "data": "synthetic",
+            "config": {"workload": desc, "envs_per_gpu": E, "agents": N, "maps": "%s first %d sorted" % (grid_name, n_maps),
+                       "obs_shape": list(env.obs_shape), "auto_reset": True, "truncate_steps": cfg["train_maxsteps"],
+                       "l2": ("flushed between timed steps (256 MiB write)" if flush is not None else
+                              "working set %.2f GB per GPU >> 126 MB L2, no flush" % (ws_bytes / 1e9)),
+                       "stats_allreduce": "NCCL per step on a side stream" if world > 1 else "none (1 GPU)"},
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": launches_timed, "clocks": clk,
+            "episode_stats": {"episodes": st[0], "mean_return": (st[1] / st[0]) if st[0] else None,
+                              "mean_length": (st[2] / st[0]) if st[0] else None,
+                              "agent_steps": st[6]},
+        }
+        if c2_extra:
+            line["c2_4096"] = c2_extra
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def make_env_kernel_only(kind, grid_name, cfg, E, device, rank):
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, load_grid_set
+    grids = load_grid_set(grid_name)
+    train = grids[:len(grids) // 2]
+    cls = VecDecGridRL if kind == "dec" else VecSuperGridRL
+    env = cls(train, cfg, num_envs=E, device=device, auto_reset=False, truncate_steps=0,
+              env_id_base=rank * E, seed=0)
+    return env, len(train)
+
+
+def run_c2_extra(torch, device):
+    """configs[1] at its literal size (4096 envs), L2 flushed between individually timed steps."""
+    kind, grid_name, E, cfg, desc = WORKLOADS["c2"]
+    env, n_maps = make_env(kind, grid_name, cfg, E, device, 0)
+    acts = gen_actions(torch, device, 32, E, cfg["numrobot"], 99)
+    env.reset(map_idx=torch.arange(E, device=device, dtype=torch.int32) % n_maps)
+    flush = torch.zeros(256 * 1024 * 1024 // 4, dtype=torch.int32, device=device)
+    ms, per, _ = timed_steps(torch, None, env, acts, 5, 100, 1, flush=flush)
+    per.sort()
+    med = per[len(per) // 2]
+    return {"workload": desc, "value": E * cfg["numrobot"] / (med * 1e-3), "unit": UNIT,
+            "ms_per_step_median": med, "l2": "flushed between timed steps"}
+
+
+def load_traffic(workload):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get(workload)
+    except Exception:
+        return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=30)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
+    ap.add_argument("--envs-per-gpu", type=int, default=0)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
