@@ -81,6 +81,17 @@ __global__ void count_free_kernel(const uint32_t* __restrict__ pos, int n_maps, 
     }
 }
 
+int64_t scratch_stats_bytes(const mcov_env* env) {
+    return align_up64((int64_t)env->num_sms * 32 * MCOV_STATS_LEN * 8, 256);
+}
+unsigned char* scratch_counter(const mcov_env* env) {
+    return env->arena + env->lay.off_scratch + scratch_stats_bytes(env);
+}
+unsigned char* scratch_dist_term(const mcov_env* env) { return scratch_counter(env) + 256; }
+unsigned char* scratch_moves(const mcov_env* env) {
+    return scratch_dist_term(env) + align_up64((int64_t)env->cfg.num_envs * 4, 256);
+}
+
 int check_ready(const mcov_env* env) {
     if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
     if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
@@ -301,11 +312,12 @@ int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_d
         l.off_visited = l.off_fo = -1;
     }
     l.off_needs_reset = off; off = align_up64(off + E, 256);
-    // scratch: stats partials (one row per CTA of the largest grid) + per-env float32 dist term
-    const int64_t max_grid = (int64_t)env->num_sms * 32;
+    // scratch: stats partial rows | CTA counter | per-env float32 dist term | per-env move scratch
     l.off_scratch = off;
-    off = align_up64(off + max_grid * MCOV_STATS_LEN * 8, 256);
+    off = align_up64(off + scratch_stats_bytes(env), 256);
+    off = align_up64(off + 256, 256);
     off = align_up64(off + E * 4, 256);
+    off = align_up64(off + E * 8, 256);
     l.total_bytes = off;
     return MCOV_OK;
 }
@@ -369,33 +381,44 @@ static int run_dec(mcov_env* env, int mode, const void* actions, int act_fmt, co
     p.reward = reward;
     p.reward64 = reward64;
     p.done = done;
-    p.bulk_ok = ((p.obs_env_floats * 4) % 16 == 0) && aligned(obs, 16);
-    double* partial = reinterpret_cast<double*>(env->arena + env->lay.off_scratch);
-    p.stats_partial = (stats && mode == mcov::MODE_STEP) ? partial : nullptr;
+    p.vec_ok = ((p.obs_env_floats * 4) % 16 == 0) && aligned(obs, 16);
+    p.phases = mcov::PH_MOVE | mcov::PH_SENSE;
+    p.stats_partial = reinterpret_cast<double*>(env->arena + env->lay.off_scratch);
+    p.stats_out = (mode == mcov::MODE_STEP) ? stats : nullptr;
+    p.counter = reinterpret_cast<unsigned int*>(scratch_counter(env));
+    p.move_scratch = reinterpret_cast<uint2*>(scratch_moves(env));
     const mcov_config& c = env->cfg;
+    const mcov_layout& l = env->lay;
     const bool extras = c.dist_reward || c.dijkstra_input || c.mini_map_rad > 0;
     cudaError_t ce;
+    if (mode == mcov::MODE_RESET && !mask && !mask_from_flags) {
+        // whole-batch reset: zero every plane with one memset instead of per-warp wipes
+        const size_t nb = (size_t)c.num_envs * l.plane_words * 4;
+        ce = cudaMemsetAsync(env->arena + l.off_visited, 0, nb, st);
+        if (ce == cudaSuccess) ce = cudaMemsetAsync(env->arena + l.off_fo, 0, nb * 2 * c.num_robots, st);
+        if (ce != cudaSuccess) return cuda_fail(ce, "cudaMemsetAsync(planes)");
+        p.skip_wipe = 1;
+    }
     if (mode == mcov::MODE_STEP && c.map_sharing) {
         ce = mcov::launch_dec_share(env, st);                     // dec_grid_rl.py:124-125
         if (ce != cudaSuccess) return cuda_fail(ce, "dec_share launch");
     }
     if (c.dist_reward && mode == mcov::MODE_STEP) {
-        // distance term uses the PRE-sensing memory at the POST-move pose: needs the moves first.
-        // handled inside launch_dec_extras(pre_sense=1) which replays the move resolution.
-        p.dist_term = reinterpret_cast<float*>(env->arena + env->lay.off_scratch +
-                                               align_up64((int64_t)env->num_sms * 32 * MCOV_STATS_LEN * 8, 256));
+        // row D11: the distance term is read from the PRE-sensing memory at the POST-move pose, so
+        // the step is split: moves -> per-robot distance maps -> sensing/reward/observation.
+        p.phases = mcov::PH_MOVE;
+        ce = mcov::launch_dec(env, p, st);
+        if (ce != cudaSuccess) return cuda_fail(ce, "dec move launch");
+        p.dist_term = reinterpret_cast<float*>(scratch_dist_term(env));
         ce = mcov::launch_dec_extras(env, nullptr, 1, st);
         if (ce != cudaSuccess) return cuda_fail(ce, "dec dist-term launch");
+        p.phases = mcov::PH_SENSE;
     }
     ce = mcov::launch_dec(env, p, st);
     if (ce != cudaSuccess) return cuda_fail(ce, "dec kernel launch");
     if (extras) {
         ce = mcov::launch_dec_extras(env, obs, 0, st);
         if (ce != cudaSuccess) return cuda_fail(ce, "dec extras launch");
-    }
-    if (p.stats_partial) {
-        ce = mcov::launch_stats_reduce(env, partial, mcov::dec_grid_size(env), stats, st);
-        if (ce != cudaSuccess) return cuda_fail(ce, "stats reduce launch");
     }
     return MCOV_OK;
 }
@@ -462,21 +485,19 @@ int mcov_step(mcov_env* env, const void* actions_dev, int action_format, float* 
     if (stats_out_dev && !aligned(stats_out_dev, 8)) return fail(MCOV_ERR_ALIGN, "stats_out misaligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool dec = env->cfg.env_type == MCOV_ENV_DEC;
-    rc = dec ? run_dec(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, 0,
-                       obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st)
-             : run_super(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, 0,
-                         obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
+    // finished / truncated envs restart in place when auto_reset is on; their obs rows become the
+    // new episode's first observation (gym auto-reset convention).  Seed: constant mixed with the
+    // shard base; the per-slot episode counter and global env id key the draw inside the kernel.
+    const uint64_t seed = 0x9E3779B97F4A7C15ull ^ (uint64_t)env->cfg.env_id_base;
+    if (dec)   // DecGridRL: the re-seed is fused into the step kernel (one launch per step)
+        return run_dec(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, seed,
+                       obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
+    rc = run_super(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, 0,
+                   obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
     if (rc) return rc;
-    if (env->cfg.auto_reset) {
-        // finished / truncated envs restart in place; their obs rows become the new episode's first
-        // observation (gym auto-reset convention).  Seed: config-independent constant mixed with the
-        // per-slot episode counter inside the kernel.
-        const uint64_t seed = 0x9E3779B97F4A7C15ull ^ (uint64_t)env->cfg.env_id_base;
-        rc = dec ? run_dec(env, mcov::MODE_RESET, nullptr, 0, nullptr, 1, nullptr, nullptr, seed,
-                           obs_out_dev, nullptr, nullptr, nullptr, nullptr, st)
-                 : run_super(env, mcov::MODE_RESET, nullptr, 0, nullptr, 1, nullptr, nullptr, seed,
-                             obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
-    }
+    if (env->cfg.auto_reset)
+        rc = run_super(env, mcov::MODE_RESET, nullptr, 0, nullptr, 1, nullptr, nullptr, seed,
+                       obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
     return rc;
 }
 

@@ -1,4 +1,5 @@
-// mcov_dec.cu — DecGridRL reset/step/observe as ONE fused sm_100a kernel.
+// mcov_dec.cu — DecGridRL reset/step/observe as ONE fused sm_100a kernel (auto-reset and episode
+// statistics included: a step is a single launch).
 //
 // Reference semantics restated here (file:line in ExistentialRobotics/MARL-Coverage):
 //   DecGridRL.step            Environments/dec_grid_rl.py:91-169
@@ -11,60 +12,35 @@
 //   reset                     dec_grid_rl.py:449-531
 //   done / percent_covered    dec_grid_rl.py:533-552
 //
-// Mapping: one CTA owns one env per loop iteration (persistent grid-stride loop); inside the CTA a
-// group of LPA lanes (16 or 32) owns one robot and its lanes own window ROWS.  All per-robot maps
-// are bit planes in HBM ("strip-major", see include/mcov.h); a window row is a <=32-bit field cut
-// from <=2 words with a funnel shift.  Newly covered cells are counted with __popc + shuffles, no
-// global atomics: every bitmap word has exactly one writer (owner election when footprints
-// overlap).  The float32 observation block of the env is assembled in shared memory and leaves
-// the SM as ONE async bulk copy (cp.async.bulk, TMA engine) straight into the torch buffer.
+// Mapping: ONE WARP owns one env per loop iteration (persistent warp-stride loop, up to 8 warps per
+// CTA, 4 CTAs per SM -> 32 envs in flight per SM, no CTA-wide barrier on the path).  Lanes < N hold
+// the robots' poses for the sequential collision-checked moves (shuffle + ballot); afterwards lanes
+// own (robot, window-row) pairs.  All per-robot maps are bit planes in HBM ("strip-major", see
+// include/mcov.h); a window row is a <=32-bit field cut from <=2 words with a funnel shift.  The
+// words under the observation window are loaded ONCE and serve both the memory update
+// (free_i/obst_i |= sensor hits) and the observation rows.  Newly covered cells are counted with
+// __popc + warp reductions, no global atomics: every bitmap word has exactly one writer (owner
+// election when footprints overlap).  The float32 observation block of the env is expanded from
+// the bit rows (4 bits -> one float4 through a 16-entry shared-memory table) and stored with
+// coalesced 128-bit streaming stores straight into the torch buffer.  The next env's header, poses
+// and actions are prefetched into registers while the current env is processed.
 #include "mcov_internal.h"
 
 namespace mcov {
 
 namespace {
 
-struct DecSmem {
-    float* stage;        // [obs_env_floats]
-    uint32_t* winF;      // [N][S] sensor-window free hits, window-relative bits
-    uint32_t* winO;      // [N][S] sensor-window obstacle hits
-    uint32_t* wallW;     // [N][S] lidar: truth wall window
-    uint32_t* posF;      // [N] final positions packed (x | y<<16)
-    int* covS;           // [N] per-robot known-free counts after this step
-    int* red;            // [32] per-warp partial new-cell counts
-    int* misc;           // [4]
-    double* stats;       // [MCOV_STATS_LEN] per-CTA running sums (thread 0 only)
-};
-
-__host__ __device__ inline size_t dec_smem_bytes(int obs_env_floats, int N, int S) {
-    size_t b = (size_t)round_up(obs_env_floats * 4, 16);
-    b += (size_t)3 * N * S * 4;
-    b += (size_t)N * 4 * 2;
-    b += 32 * 4 + 4 * 4;
-    b += MCOV_STATS_LEN * 8;
-    return round_up((int)b, 16);
-}
-
-__device__ __forceinline__ DecSmem carve(unsigned char* base, int obs_env_floats, int N, int S) {
-    DecSmem s;
-    s.stage = reinterpret_cast<float*>(base);
-    unsigned char* q = base + round_up(obs_env_floats * 4, 16);
-    s.stats = reinterpret_cast<double*>(q); q += MCOV_STATS_LEN * 8;
-    s.winF = reinterpret_cast<uint32_t*>(q); q += N * S * 4;
-    s.winO = reinterpret_cast<uint32_t*>(q); q += N * S * 4;
-    s.wallW = reinterpret_cast<uint32_t*>(q); q += N * S * 4;
-    s.posF = reinterpret_cast<uint32_t*>(q); q += N * 4;
-    s.covS = reinterpret_cast<int*>(q); q += N * 4;
-    s.red = reinterpret_cast<int*>(q); q += 32 * 4;
-    s.misc = reinterpret_cast<int*>(q);
-    return s;
-}
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int MAX_WARPS = 8;
 
 __device__ __forceinline__ uint32_t pack_xy(int x, int y) {
     return (uint32_t)(x & 0xffff) | ((uint32_t)(y & 0xffff) << 16);
 }
 __device__ __forceinline__ int unpack_x(uint32_t v) { return (int)(int16_t)(v & 0xffffu); }
 __device__ __forceinline__ int unpack_y(uint32_t v) { return (int)(int16_t)(v >> 16); }
+
+// floor(k / d) for k < 2^26, d <= 64, magic = ceil(2^32 / d)
+__device__ __forceinline__ int fast_div(int k, uint32_t magic) { return (int)__umulhi((uint32_t)k, magic); }
 
 // Draws map + start poses on the device: uniform map, uniform distinct walkable cells by rejection
 // (same distribution as dec_grid_rl.py:462-502; not numpy's Mersenne-Twister stream).
@@ -108,216 +84,323 @@ __device__ void draw_reset(const DecParams& p, int e, uint32_t episode, uint32_t
     for (; placed < p.N; ++placed) posS[placed] = pack_xy(0, 0);
 }
 
-template <int LPA>
-__global__ void __launch_bounds__(LPA == 16 ? 256 : 1024, LPA == 16 ? 4 : 1)
-dec_env_kernel(const DecParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const DecSmem sm = carve(smem_raw, p.obs_env_floats, p.N, p.S);
+// Raw (untouched) register copies of the next env's inputs: nothing is computed on them until the
+// env is processed, so the loads stay in flight behind the current env's work.
+struct Prefetch {
+    uint32_t pos;        // lane < N: packed pose
+    uint32_t act8;       // lane < N: per-robot move (U8 format)
+    long long act64;     // base-4 joint action (I64 format)
+    int map_idx;
+    uint32_t shown;
+};
 
-    const int tid = threadIdx.x;
-    const int lane = tid & 31;
-    const int warp = tid >> 5;
-    const int nwarps = (blockDim.x + 31) >> 5;
-    const int lg = tid % LPA;             // lane within the robot group
-    const int i = tid / LPA;              // robot owned by this group
-    const int gshift = lane & ~(LPA - 1); // first warp lane of this group
-    const bool gvalid = i < p.N;          // blockDim is rounded up to whole warps
-    const uint32_t gbits = LPA == 32 ? 0xffffffffu : 0xffffu;
+__device__ __forceinline__ Prefetch load_prefetch(const DecParams& p, int e, int lane) {
+    Prefetch f;
+    const unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
+    const EnvHead* head = reinterpret_cast<const EnvHead*>(hrec);
+    f.map_idx = head->map_idx;
+    f.shown = head->flags;
+    f.pos = 0;
+    f.act8 = 0;
+    f.act64 = 0;
+    if (lane < p.N) f.pos = reinterpret_cast<const uint32_t*>(hrec + p.off_pos)[lane];
+    if (p.mode == MODE_STEP) {
+        if (p.act_fmt == MCOV_ACT_I64_BASE4) f.act64 = reinterpret_cast<const long long*>(p.actions)[e];
+        else if (lane < p.N) f.act8 = reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * p.N + lane];
+    }
+    return f;
+}
+
+struct WarpSmem {
+    double* stats;       // [MCOV_STATS_LEN] running sums of this warp (lane 0 only)
+    uint32_t* rows;      // [N*C*ow (+pad)] observation bit rows, flat [robot][channel][row]
+    uint32_t* winF;      // [N*S] sensor-window free hits, window-relative bits
+    uint32_t* winO;      // [N*S] sensor-window obstacle hits
+    uint32_t* posF;      // [N] poses after the moves
+    int* covS;           // [N] per-robot newly known-free cells of this step
+    uint32_t* wallW;     // [N*S] lidar: truth wall window
+};
+
+__device__ __forceinline__ WarpSmem carve(unsigned char* base, const DecParams& p) {
+    WarpSmem s;
+    s.stats = reinterpret_cast<double*>(base);
+    s.rows = reinterpret_cast<uint32_t*>(base + MCOV_STATS_LEN * 8);
+    s.winF = s.rows + p.rows_words;
+    s.winO = s.winF + p.N * p.S;
+    s.posF = s.winO + p.N * p.S;
+    s.covS = reinterpret_cast<int*>(s.posF + p.N);
+    s.wallW = reinterpret_cast<uint32_t*>(s.covS + p.N);
+    return s;
+}
+
+// One pass over env e in `mode`.  Returns true when a finished env must be re-seeded in place by a
+// second (MODE_RESET) pass of the same warp (fused auto-reset).
+template <bool LIDAR>
+__device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm, const float4* lut,
+                                         const int e, const int mode, const Prefetch& cur,
+                                         const int lane) {
     const int N = p.N, S = p.S, R = p.R, W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips;
-    const int ow = p.ow, ego = p.ego, C = p.C;
-    const int mode = p.mode;
+    const int PW = p.g.PW;
+    const int ow = p.ow, ego = p.ego, C = p.C, rad = p.rad, RW = p.RW;
 
-    double* st_acc = sm.stats;
-    if (tid == 0)
-        for (int k = 0; k < MCOV_STATS_LEN; ++k) st_acc[k] = 0.0;
+    unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
+    EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
+    uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
+    int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
+    uint32_t* hadj = reinterpret_cast<uint32_t*>(hrec + p.off_adj);
+    uint2* fo_e = p.fo + (size_t)e * N * PW;
+    uint32_t* vis = p.visited + (size_t)e * PW;
 
-    for (int e = blockIdx.x; e < p.E; e += gridDim.x) {
-        unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
-        EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
-        uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
-        int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
-        uint32_t* hadj = reinterpret_cast<uint32_t*>(hrec + p.off_adj);
-        uint2* fo_i = p.fo + ((size_t)e * N + (gvalid ? i : 0)) * p.g.PW;
-        uint32_t* vis = p.visited + (size_t)e * p.g.PW;
-
-        if (mode == MODE_RESET) {
-            int act = 1;
-            if (p.mask) act = p.mask[e];
-            else if (p.mask_from_flags) act = p.needs_reset[e];
-            if (!act) continue;                                   // CTA-uniform
-        }
-
-        // ------------------------------------------------------------------ phase A
-        const bool fresh = (mode == MODE_RESET);
-        int map_idx;
-        uint32_t shown = 0;
-        if (fresh) {
-            if (tid == 0) bulk_wait_read_all();                   // stage/posF reuse
-            if (tid == 0) {
-                int mi;
-                draw_reset(p, e, head->episode, sm.posF, &mi);
-                sm.misc[0] = mi;
-            }
+    const bool fresh = (mode == MODE_RESET);
+    int map_idx;
+    uint32_t shown, myv;
+    if (fresh) {
+        int mi = 0;
+        if (lane == 0) draw_reset(p, e, head->episode, sm.posF, &mi);
+        map_idx = __shfl_sync(FULL, mi, 0);
+        if (!p.skip_wipe) {
             // wipe this env's planes (dec_grid_rl.py:505-514) with 128-bit stores
-            {
-                uint4* z = reinterpret_cast<uint4*>(p.fo + (size_t)e * N * p.g.PW);
-                const int n16 = N * p.g.PW / 2;
-                for (int k = tid; k < n16; k += blockDim.x) z[k] = make_uint4(0, 0, 0, 0);
-                uint4* zv = reinterpret_cast<uint4*>(vis);
-                for (int k = tid; k < p.g.PW / 4; k += blockDim.x) zv[k] = make_uint4(0, 0, 0, 0);
-            }
-            __syncthreads();
-            map_idx = sm.misc[0];
+            uint4* z = reinterpret_cast<uint4*>(fo_e);
+            const int n16 = N * (PW / 2);
+            for (int k = lane; k < n16; k += 32) z[k] = make_uint4(0, 0, 0, 0);
+            uint4* zv = reinterpret_cast<uint4*>(vis);
+            for (int k = lane; k < PW / 4; k += 32) zv[k] = make_uint4(0, 0, 0, 0);
+        }
+        __syncwarp();
+        myv = lane < N ? sm.posF[lane] : 0u;
+        shown = 0;
+    } else {
+        map_idx = cur.map_idx;
+        shown = cur.shown;
+        myv = cur.pos;
+    }
+    const uint32_t* wall = p.wall + (size_t)map_idx * PW;
+    const uint32_t* tpos = p.pos + (size_t)map_idx * PW;
+
+    // early loads for the bookkeeping at the end of the pass (kept in flight until then)
+    int cs0 = 0, fc = 1;
+    double th = 0.0, epr0 = 0.0;
+    if (mode == MODE_STEP && lane == 0) {
+        cs0 = head->currstep;
+        th = head->done_thresh;
+        epr0 = head->ep_return;
+        fc = __ldg(p.free_counts + map_idx);
+    }
+    int cov_old = 0;
+    if (mode == MODE_STEP && lane < N) cov_old = hcov[lane];
+
+    int px = unpack_x(myv), py = unpack_y(myv);
+    int ncoll = 0;
+    bool sentinel = false;
+    if (mode == MODE_STEP) {
+        // ---- action decode (dec_grid_rl.py:110-117) ------------------------------------------
+        int u;
+        if (p.act_fmt == MCOV_ACT_I64_BASE4) {
+            sentinel = (cur.act64 == -1);
+            u = (int)((cur.act64 >> (2 * (lane & 31))) & 3);
         } else {
-            map_idx = head->map_idx;
-            shown = head->flags;
+            u = (int)(cur.act8 & 3u);
         }
-        const uint32_t* wall = p.wall + (size_t)map_idx * p.g.PW;
-        const uint32_t* tpos = p.pos + (size_t)map_idx * p.g.PW;
-
-        int px = 0, py = 0;
-        if (lg < N) {
-            const uint32_t v = fresh ? sm.posF[lg] : hpos[lg];
-            px = unpack_x(v);
-            py = unpack_y(v);
-        }
-
-        int ncoll = 0;
-        bool sentinel = false;
-        if (mode == MODE_STEP) {
-            // ---- action decode (dec_grid_rl.py:110-117) ------------------------------------
-            int u = 0;
-            if (p.act_fmt == MCOV_ACT_I64_BASE4) {
-                const long long a = reinterpret_cast<const long long*>(p.actions)[e];
-                sentinel = (a == -1);
-                u = (int)((a >> (2 * (lg & 31))) & 3);
-            } else if (lg < N) {
-                u = reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * N + lg] & 3;
-            }
-            if (!sentinel) {
-                // ---- sequential, collision-checked moves (dec_grid_rl.py:128-145,171-204) ----
-                // Dec table: 0:x+1  1:y+1  2:x-1  3:y-1
-                const int tx = px + (u == 0) - (u == 2);
-                const int ty = py + (u == 1) - (u == 3);
-                int blocked0 = 1;
-                if (lg < N && tx >= 0 && tx < W && ty >= 0 && ty < L)
-                    blocked0 = get_bit(wall, Wp, tx, ty);
-                for (int k = 0; k < N; ++k) {
-                    const int txk = __shfl_sync(0xffffffffu, tx, k, LPA);
-                    const int tyk = __shfl_sync(0xffffffffu, ty, k, LPA);
-                    const int blk = __shfl_sync(0xffffffffu, blocked0, k, LPA);
-                    const bool hit = (lg < N) && px == txk && py == tyk;
-                    const uint32_t b = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
-                    if (!blk && b == 0) {
-                        if (lg == k) { px = txk; py = tyk; }
-                        shown |= 1u << k;
-                    } else {
-                        ++ncoll;
-                    }
+        if (!sentinel && (p.phases & PH_MOVE)) {
+            // ---- sequential, collision-checked moves (dec_grid_rl.py:128-145,171-204) --------
+            // Dec table: 0:x+1  1:y+1  2:x-1  3:y-1
+            const int tx = px + (u == 0) - (u == 2);
+            const int ty = py + (u == 1) - (u == 3);
+            int blocked0 = 1;
+            if (lane < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
+            for (int k = 0; k < N; ++k) {
+                const int txk = __shfl_sync(FULL, tx, k);
+                const int tyk = __shfl_sync(FULL, ty, k);
+                const int blk = __shfl_sync(FULL, blocked0, k);
+                const bool hit = (lane < N) && px == txk && py == tyk;
+                const uint32_t b = __ballot_sync(FULL, hit);
+                if (!blk && b == 0) {
+                    if (lane == k) { px = txk; py = tyk; }
+                    shown |= 1u << k;
+                } else {
+                    ++ncoll;
                 }
             }
+        } else if (!sentinel) {
+            // moves were resolved by an earlier PH_MOVE launch (dist_reward pipeline)
+            const uint2 ms = p.move_scratch[e];
+            ncoll = (int)ms.x;
+            shown = ms.y;
         }
-        // publish poses for cross-robot lookups; group 0 also persists them
-        if (i == 0 && lg < N) {
-            const uint32_t v = pack_xy(px, py);
-            sm.posF[lg] = v;
-            if (mode != MODE_OBSERVE) hpos[lg] = v;
-        }
-        const int xi = __shfl_sync(0xffffffffu, px, i, LPA);
-        const int yi = __shfl_sync(0xffffffffu, py, i, LPA);
+    }
+    // publish poses for cross-robot lookups and persist them
+    const uint32_t newv = pack_xy(px, py);
+    if (lane < N) {
+        sm.posF[lane] = newv;
+        sm.covS[lane] = 0;
+        if (mode != MODE_OBSERVE && (fresh || newv != myv)) hpos[lane] = newv;
+    }
 
-        // ---- communication graph (dec_grid_rl.py:374-391): Chebyshev ball, diagonal included --
-        if (p.want_adj && mode != MODE_OBSERVE) {
-            const bool link = (lg < N) && max(abs(px - xi), abs(py - yi)) <= p.comm_radius;
-            const uint32_t b = (__ballot_sync(0xffffffffu, link) >> gshift) & gbits;
-            if (lg == 0 && gvalid) hadj[i] = b;
+    // ---- communication graph (dec_grid_rl.py:374-391): Chebyshev ball, diagonal included ------
+    if (mode != MODE_OBSERVE && (p.comm_radius > 0 || fresh)) {
+        uint32_t myadj = 1u << lane;
+        if (p.comm_radius > 0) {
+            for (int i = 0; i < N; ++i) {
+                const int xi = __shfl_sync(FULL, px, i), yi = __shfl_sync(FULL, py, i);
+                const bool link = (lane < N) && max(abs(px - xi), abs(py - yi)) <= p.comm_radius;
+                const uint32_t b = __ballot_sync(FULL, link);
+                if (lane == i) myadj = b;
+            }
         }
+        if (lane < N) hadj[lane] = myadj;
+    }
+    if (mode == MODE_STEP && !(p.phases & PH_SENSE)) {
+        if (lane == 0) p.move_scratch[e] = make_uint2((uint32_t)ncoll, shown);
+        return false;
+    }
+    __syncwarp();
 
-        const bool do_sense = (mode == MODE_RESET) || (mode == MODE_STEP && !sentinel);
-        bool near_other = false;
-        if (do_sense && gvalid) {
-            // can another robot's sensor rows share a bitmap word with mine?
-            near_other = (lg < N) && (lg != i) && abs(px - xi) <= 2 * R && abs(py - yi) < S + 32;
-            const int y0 = yi - R;
-            if (p.sensor == MCOV_SENSOR_SQUARE) {
-                // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
-                for (int r = lg; r < S; r += LPA) {
-                    const int x = xi - R + r;
-                    uint32_t f = 0, o = 0;
-                    if (x >= 0 && x < W) {
-                        o = read_window(wall, Wp, strips, x, y0, S);
-                        if (p.single_tool) f = (r == R) ? (1u << R) : 0u;      // dec_grid_rl.py:233-234
-                        else f = read_window(tpos, Wp, strips, x, y0, S);
-                    }
-                    sm.winF[i * S + r] = f;
-                    sm.winO[i * S + r] = o;
+    const bool do_sense = fresh || (mode == MODE_STEP && !sentinel);
+    bool near_other = false;
+    if (do_sense) {
+        // can another robot's sensor rows share a bitmap word with mine?
+        if (lane < N)
+            for (int j = 0; j < N; ++j) {
+                const uint32_t pj = sm.posF[j];
+                near_other |= (j != lane) && abs(px - unpack_x(pj)) <= 2 * R && abs(py - unpack_y(pj)) < S + 32;
+            }
+        if (!LIDAR) {
+            // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
+            for (int idx = lane; idx < N * S; idx += 32) {
+                const int i = fast_div(idx, p.s_magic), r = idx - i * S;
+                const uint32_t pi = sm.posF[i];
+                const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
+                uint32_t f = 0, o = 0;
+                if (x >= 0 && x < W) {
+                    o = read_window(wall, Wp, strips, x, y0, S);
+                    if (p.single_tool) f = (r == R) ? (1u << R) : 0u;       // dec_grid_rl.py:233-234
+                    else f = read_window(tpos, Wp, strips, x, y0, S);
                 }
-            } else {
-                // lidar.py:16-65 — stage the truth wall window, then march beams in float64
-                for (int r = lg; r < S; r += LPA) {
-                    const int x = xi - R + r;
-                    sm.wallW[i * S + r] = (x >= 0 && x < W) ? read_window(wall, Wp, strips, x, y0, S)
-                                                            : 0xffffffffu;
-                    sm.winF[i * S + r] = 0;
-                    sm.winO[i * S + r] = 0;
+                sm.winF[idx] = f;
+                sm.winO[idx] = o;
+            }
+        } else {
+            // lidar.py:16-65 — stage the truth wall window, then march beams in float64
+            for (int idx = lane; idx < N * S; idx += 32) {
+                const int i = fast_div(idx, p.s_magic), r = idx - i * S;
+                const uint32_t pi = sm.posF[i];
+                const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
+                sm.wallW[idx] = (x >= 0 && x < W) ? read_window(wall, Wp, strips, x, y0, S) : 0xffffffffu;
+                sm.winF[idx] = 0;
+                sm.winO[idx] = 0;
+            }
+            __syncwarp();
+            const double rng = (double)R;
+            for (int idx = lane; idx < N * p.n_lasers; idx += 32) {
+                const int i = idx / p.n_lasers, l = idx - i * p.n_lasers;
+                const uint32_t pi = sm.posF[i];
+                const int xi = unpack_x(pi), yi = unpack_y(pi);
+                const double xinc = __ldg(p.beams + 3 * l), yinc = __ldg(p.beams + 3 * l + 1),
+                             dinc = __ldg(p.beams + 3 * l + 2);
+                double cx = (double)xi, cy = (double)yi, dist = 0.0;
+                int rx, ry;
+                bool walk;
+                while (true) {
+                    const bool inside = cx >= 0.0 && cy >= 0.0 && cx < (double)W && cy < (double)L;
+                    rx = __double2int_rz(cx) - (xi - R);
+                    ry = __double2int_rz(cy) - (yi - R);
+                    const bool inwin = rx >= 0 && rx < S && ry >= 0 && ry < S;
+                    walk = inside && inwin && !((sm.wallW[i * S + rx] >> ry) & 1u);
+                    if (!(walk && dist < rng)) break;
+                    atomicOr(&sm.winF[i * S + rx], 1u << ry);
+                    cx += xinc;
+                    cy += yinc;
+                    dist += dinc;
                 }
+                if (rx >= 0 && rx < S && ry >= 0 && ry < S) {
+                    if (walk) atomicOr(&sm.winF[i * S + rx], 1u << ry);
+                    else atomicOr(&sm.winO[i * S + rx], 1u << ry);
+                }
+            }
+            if (p.single_tool) {
                 __syncwarp();
-                const double rng = (double)R;
-                for (int l = lg; l < p.n_lasers; l += LPA) {
-                    const double xinc = p.beams[3 * l], yinc = p.beams[3 * l + 1], dinc = p.beams[3 * l + 2];
-                    double cx = (double)xi, cy = (double)yi, dist = 0.0;
-                    int rx, ry;
-                    bool walk;
-                    while (true) {
-                        const bool inside = cx >= 0.0 && cy >= 0.0 && cx < (double)W && cy < (double)L;
-                        rx = __double2int_rz(cx) - (xi - R);
-                        ry = __double2int_rz(cy) - y0;
-                        const bool inwin = rx >= 0 && rx < S && ry >= 0 && ry < S;
-                        walk = inside && inwin && !((sm.wallW[i * S + rx] >> ry) & 1u);
-                        if (!(walk && dist < rng)) break;
-                        atomicOr(&sm.winF[i * S + rx], 1u << ry);
-                        cx += xinc;
-                        cy += yinc;
-                        dist += dinc;
-                    }
-                    if (rx >= 0 && rx < S && ry >= 0 && ry < S) {
-                        if (walk) atomicOr(&sm.winF[i * S + rx], 1u << ry);
-                        else atomicOr(&sm.winO[i * S + rx], 1u << ry);
-                    }
-                }
-                if (p.single_tool) {
-                    __syncwarp();
-                    for (int r = lg; r < S; r += LPA) sm.winF[i * S + r] = (r == R) ? (1u << R) : 0u;
+                for (int idx = lane; idx < N * S; idx += 32) {
+                    const int i = fast_div(idx, p.s_magic), r = idx - i * S;
+                    sm.winF[idx] = (r == R) ? (1u << R) : 0u;
                 }
             }
         }
-        if (tid == 0 && !fresh) bulk_wait_read_all();             // previous env's obs left smem
-        const int overlap = __syncthreads_or(near_other ? 1 : 0); // sync #1: windows + poses published
+    }
+    const bool overlap = __any_sync(FULL, near_other);      // also orders winF/winO/posF for the warp
 
-        // ------------------------------------------------------------------ phase B
-        int cnt = 0, covnew = 0;
-        if (do_sense && gvalid) {
-            const int y0 = yi - R;
-            const int s0 = y0 >> 5;
-            const bool straddle = (y0 & 31) + S > 32;
-            for (int r = lg; r < S; r += LPA) {
-                const int x = xi - R + r;
-                if (x < 0 || x >= W) continue;
-                uint32_t fw[2], owd[2];
-                split_words(sm.winF[i * S + r], y0, fw[0], fw[1]);
-                split_words(sm.winO[i * S + r], y0, owd[0], owd[1]);
+    // ---- fused memory update + observation rows ---------------------------------------------
+    // Lane slot = (robot i, row a2 of the (2*rad+1)-row band around it), rad = max(ego, R).  The
+    // <=2 interleaved {free_i, obst_i} words under the band row are loaded once; rows inside the
+    // sensor range get the hits ORed in and written back; rows inside the egocentric window
+    // produce the observation bit rows.  All loads of both slots are issued before any store.
+    int cnt = 0;
+    const int total = N * RW;
+    const uint32_t wm_ow = low_mask(ow);
+    for (int base = 0; base < total; base += 64) {
+        uint2 lo[2], hi[2];
+        uint32_t vlo[2], vhi[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int idx = base + 32 * u + lane;
+            lo[u] = make_uint2(0, 0);
+            hi[u] = make_uint2(0, 0);
+            vlo[u] = 0;
+            vhi[u] = 0;
+            if (idx < total && !fresh) {
+                const int i = fast_div(idx, p.rw_magic), a2 = idx - i * RW;
+                const uint32_t pi = sm.posF[i];
+                const int xi = unpack_x(pi), yi = unpack_y(pi);
+                const int x = xi - rad + a2;
+                if (x >= 0 && x < W) {
+                    const int y0r = yi - rad, s0 = y0r >> 5;
+                    const bool in0 = s0 >= 0 && s0 < strips;
+                    const bool in1 = ((y0r & 31) + RW > 32) && s0 + 1 >= 0 && s0 + 1 < strips;
+                    const uint2* fo_i = fo_e + (size_t)i * PW;
+                    const int w0 = s0 * Wp + x;
+                    if (in0) lo[u] = fo_i[w0];
+                    if (in1) hi[u] = fo_i[w0 + Wp];
+                    if (do_sense && abs(x - xi) <= R) {
+                        const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
+                        if (in0 && s0 >= ys0) vlo[u] = vis[w0];
+                        if (in1 && s0 + 1 <= ys1) vhi[u] = vis[w0 + Wp];
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int idx = base + 32 * u + lane;
+            if (idx >= total) continue;
+            const int i = fast_div(idx, p.rw_magic), a2 = idx - i * RW;
+            const uint32_t pi = sm.posF[i];
+            const int xi = unpack_x(pi), yi = unpack_y(pi);
+            const int x = xi - rad + a2;
+            const bool inx = x >= 0 && x < W;
+            const int y0r = yi - rad, s0 = y0r >> 5, sh = y0r & 31;
+            uint2 nlo = lo[u], nhi = hi[u];
+            if (inx && do_sense && abs(x - xi) <= R) {
+                const bool in0 = s0 >= 0 && s0 < strips;
+                const bool in1 = (sh + RW > 32) && s0 + 1 >= 0 && s0 + 1 < strips;
+                const int r = x - xi + R;
+                uint32_t f0, f1, o0, o1;
+                split_words(sm.winF[i * S + r] << (rad - R), y0r, f0, f1);
+                split_words(sm.winO[i * S + r] << (rad - R), y0r, o0, o1);
+                uint2* fo_i = fo_e + (size_t)i * PW;
+                const int w0 = s0 * Wp + x;
+                // per-robot memory: free_i |= hits, obst_i |= hits  (dec_grid_rl.py:231-236)
+                nlo = make_uint2(lo[u].x | f0, lo[u].y | o0);
+                nhi = make_uint2(hi[u].x | f1, hi[u].y | o1);
+                const int cn = __popc(f0 & ~lo[u].x) + __popc(f1 & ~hi[u].x);
+                if (in0 && (nlo.x != lo[u].x || nlo.y != lo[u].y)) fo_i[w0] = nlo;
+                if (in1 && (nhi.x != hi[u].x || nhi.y != hi[u].y)) fo_i[w0 + Wp] = nhi;
+                if (cn) atomicAdd(&sm.covS[i], cn);                 // shared-memory atomic
+                // union "visited" plane: exactly one writer per word (dec_grid_rl.py:243-256)
+                const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
                     const int s = s0 + k;
-                    if (s < 0 || s >= strips || (k == 1 && !straddle)) continue;
-                    const int widx = s * Wp + x;
-                    // per-robot memory: free_i |= hits, obst_i |= hits  (dec_grid_rl.py:231-236)
-                    const uint2 old = fresh ? make_uint2(0, 0) : fo_i[widx];
-                    const uint32_t nf = old.x | fw[k], no = old.y | owd[k];
-                    covnew += __popc(fw[k] & ~old.x);
-                    if (nf != old.x || no != old.y) fo_i[widx] = make_uint2(nf, no);
-                    // union "visited" plane: exactly one writer per word (dec_grid_rl.py:243-256)
-                    uint32_t comb = fw[k];
+                    if (!(k == 0 ? in0 : in1) || s < ys0 || s > ys1) continue;
+                    uint32_t comb = k == 0 ? f0 : f1;
                     bool owner = true;
                     if (overlap) {
                         for (int j = 0; j < N; ++j) {
@@ -327,140 +410,204 @@ dec_env_kernel(const DecParams p) {
                             if (rj < 0 || rj >= S) continue;
                             const int y0j = unpack_y(pj) - R;
                             const int s0j = y0j >> 5;
-                            uint32_t lo, hi;
-                            split_words(sm.winF[j * S + rj], y0j, lo, hi);
-                            if (s == s0j) { comb |= lo; owner &= (j > i); }
-                            else if (s == s0j + 1 && (y0j & 31) + S > 32) { comb |= hi; owner &= (j > i); }
+                            uint32_t jl, jh;
+                            split_words(sm.winF[j * S + rj], y0j, jl, jh);
+                            if (s == s0j) { comb |= jl; owner &= (j > i); }
+                            else if (s == s0j + 1 && (y0j & 31) + S > 32) { comb |= jh; owner &= (j > i); }
                         }
                     }
                     if (owner) {
-                        const uint32_t vold = fresh ? 0u : vis[widx];
+                        const uint32_t vold = k == 0 ? vlo[u] : vhi[u];
                         const uint32_t nb = comb & ~vold;
                         cnt += __popc(nb);
-                        if (nb) vis[widx] = vold | comb;
+                        if (nb) vis[w0 + k * Wp] = vold | comb;
                     }
                 }
             }
-        }
-        // per-robot known-free count (percent_covered sums over robots, quirk A.3.3)
-#pragma unroll
-        for (int d = LPA / 2; d > 0; d >>= 1) covnew += __shfl_xor_sync(0xffffffffu, covnew, d, LPA);
-        if (lg == 0 && gvalid) {
-            const int c = (fresh ? 0 : hcov[i]) + covnew;
-            sm.covS[i] = c;
-            if (covnew != 0 || fresh) hcov[i] = c;
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
-        if (lane == 0) sm.red[warp] = cnt;
-
-        // ---- egocentric observation rows (dec_grid_rl.py:334-347) -> float32 staging -----------
-        if (C > 3 && gvalid) {
-            float* z = sm.stage + (size_t)(i * C + 3) * ow * ow;
-            for (int k = lg; k < (C - 3) * ow * ow; k += LPA) z[k] = 0.0f;
-        }
-        if (gvalid) {
-            const int y0e = yi - ego;
-            const uint32_t wm = low_mask(ow);
-            for (int a = lg; a < ow; a += LPA) {
-                const int x = xi - ego + a;
-                uint32_t bR = 0, bF = 0, bO = 0;
-                if (x >= 0 && x < W) {
-                    if (!fresh) {
-                        const uint2 w2 = read_window2(fo_i, Wp, strips, x, y0e, ow);
-                        bF = w2.x;
-                        bO = w2.y;
-                    }
-                    if (do_sense) {
-                        const int r = a - (ego - R);
-                        if (r >= 0 && r < S) {
-                            bF |= shift_bits(sm.winF[i * S + r], ego - R) & wm;
-                            bO |= shift_bits(sm.winO[i * S + r], ego - R) & wm;
-                        }
-                    }
-                    // layer 0 shows every robot that has moved at least once (quirk A.3.4)
-                    for (int j = 0; j < N; ++j) {
-                        if (!((shown >> j) & 1u)) continue;
-                        const uint32_t pj = sm.posF[j];
-                        const int d = unpack_y(pj) - y0e;
-                        if (unpack_x(pj) == x && d >= 0 && d < ow) bR |= 1u << d;
-                    }
-                }
-                float* row = sm.stage + ((size_t)(i * C) * ow + a) * ow;
-                for (int b = 0; b < ow; ++b) {
-                    row[b] = ((bR >> b) & 1u) ? 1.0f : 0.0f;
-                    row[ow * ow + b] = ((bF >> b) & 1u) ? 1.0f : 0.0f;
-                    row[2 * ow * ow + b] = ((bO >> b) & 1u) ? 1.0f : 0.0f;
-                }
-            }
-        }
-        fence_proxy_async_smem();
-        __syncthreads();                                          // sync #2: stage + partials ready
-
-        // ------------------------------------------------------------------ phase C
-        float* obs_e = p.obs + (size_t)e * p.obs_env_floats;
-        if (!p.bulk_ok) {
-            for (int k = tid; k < p.obs_env_floats; k += blockDim.x) obs_e[k] = sm.stage[k];
-        }
-        if (tid == 0) {
-            if (p.bulk_ok) bulk_store_s2g(obs_e, sm.stage, (uint32_t)p.obs_env_floats * 4u);
-            if (mode == MODE_STEP) {
-                double r = 0.0;
-                int dn = 0;
-                if (sentinel) {
-                    dn = 1;                                        // dec_grid_rl.py:105-107
-                } else {
-                    for (int k = 0; k < ncoll; ++k) r -= p.cp;     // dec_grid_rl.py:185-204
-                    int newc = 0;
-                    for (int w = 0; w < nwarps; ++w) newc += sm.red[w];
-                    double obs_r = (double)newc;
-                    if (p.dist_term) obs_r = (double)p.dist_term[e] + (double)newc;   // row D11
-                    r += obs_r;
-                    const int cs = head->currstep + 1;             // :154
-                    int covsum = 0;
-                    for (int j = 0; j < N; ++j) covsum += sm.covS[j];
-                    const double pct = (double)covsum / (double)p.free_counts[map_idx];
-                    double th = head->done_thresh;
-                    const bool full = fmin(th, 1.0) <= pct;        // :156-157, :540-546
-                    if (full) { r += p.terminal; th += p.done_incr; dn = 1; }
-                    else if (cs == p.maxsteps) dn = 1;
-                    const double epr = head->ep_return + r;
-                    head->currstep = cs;
-                    head->flags = shown;
-                    head->done_thresh = th;
-                    head->ep_return = epr;
-                    const bool trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
-                    st_acc[4] += (double)ncoll;
-                    st_acc[5] += (double)newc;
-                    st_acc[6] += (double)N;
-                    if (dn || trunc) {
-                        st_acc[0] += 1.0;
-                        st_acc[1] += epr;
-                        st_acc[2] += (double)cs;
-                        st_acc[3] += pct;
-                    }
-                    p.needs_reset[e] = (dn || trunc) ? 1 : 0;
-                }
-                if (sentinel) p.needs_reset[e] = 1;
-                p.reward[e] = (float)r;
-                if (p.reward64) p.reward64[e] = r;
-                p.done[e] = (uint8_t)dn;
-            } else if (mode == MODE_RESET) {
-                head->currstep = 0;                                // :479
-                head->map_idx = map_idx;
-                head->flags = 0;                                   // _robot_pad starts empty (:487)
-                head->episode = head->episode + 1;
-                head->ep_return = 0.0;
-                p.needs_reset[e] = 0;
+            // egocentric observation rows (dec_grid_rl.py:334-347); layer 0 is filled below
+            const int a = x - (xi - ego);
+            if (a >= 0 && a < ow) {
+                const uint32_t bF = (__funnelshift_r(nlo.x, nhi.x, sh) >> (rad - ego)) & wm_ow;
+                const uint32_t bO = (__funnelshift_r(nlo.y, nhi.y, sh) >> (rad - ego)) & wm_ow;
+                uint32_t* rw = sm.rows + (size_t)(i * C) * ow + a;
+                rw[0] = 0;
+                rw[ow] = bF;
+                rw[2 * ow] = bO;
             }
         }
     }
-    if (tid == 0) {
-        bulk_wait_all();
-        if (p.stats_partial) {
-#pragma unroll
-            for (int k = 0; k < MCOV_STATS_LEN; ++k)
-                p.stats_partial[(size_t)blockIdx.x * MCOV_STATS_LEN + k] = st_acc[k];
+    __syncwarp();
+    // layer 0 shows every robot that has moved at least once (quirk A.3.4): one lane per
+    // (viewer i, shown robot j) pair
+    for (int idx = lane; idx < N * N; idx += 32) {
+        const int i = fast_div(idx, p.n_magic), j = idx - i * N;
+        if (!((shown >> j) & 1u)) continue;
+        const uint32_t pi = sm.posF[i], pj = sm.posF[j];
+        const int a = unpack_x(pj) - (unpack_x(pi) - ego), b = unpack_y(pj) - (unpack_y(pi) - ego);
+        if (a >= 0 && a < ow && b >= 0 && b < ow) atomicOr(&sm.rows[(size_t)(i * C) * ow + a], 1u << b);
+    }
+
+    // ---- reward / termination bookkeeping ------------------------------------------------------
+    cnt = __reduce_add_sync(FULL, cnt);
+    int covsum = 0;
+    if (mode != MODE_OBSERVE) {
+        int c = 0;
+        if (lane < N) {
+            const int dn = sm.covS[lane];
+            c = cov_old + dn;
+            if (fresh || dn != 0) hcov[lane] = c;                  // per-robot known-free count
+        }
+        covsum = __reduce_add_sync(FULL, c);
+    }
+    bool again = false;
+    if (mode == MODE_STEP) {
+        int flag = 0;
+        if (lane == 0) {
+            double r = 0.0;
+            int dn = 0, nr = 0;
+            if (sentinel) {
+                dn = 1;                                            // dec_grid_rl.py:105-107
+                nr = 1;
+            } else {
+                for (int k = 0; k < ncoll; ++k) r -= p.cp;         // dec_grid_rl.py:185-204
+                double obs_r = (double)cnt;
+                if (p.dist_term) obs_r = (double)p.dist_term[e] + (double)cnt;   // row D11
+                r += obs_r;
+                const int cs = cs0 + 1;                            // :154
+                // percent_covered sums over robots (quirk A.3.3); min(thresh, 1) <= pct  (:156-157)
+                bool full;
+                if (th >= 1.0) full = covsum >= fc;                // exact: c/f >= 1  <=>  c >= f
+                else full = th <= (double)covsum / (double)fc;
+                if (full) { r += p.terminal; th += p.done_incr; dn = 1; head->done_thresh = th; }
+                else if (cs == p.maxsteps) dn = 1;
+                const double epr = epr0 + r;
+                head->currstep = cs;
+                head->flags = shown;
+                head->ep_return = epr;
+                const bool trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
+                sm.stats[4] += (double)ncoll;
+                sm.stats[5] += (double)cnt;
+                sm.stats[6] += (double)N;
+                if (dn || trunc) {
+                    sm.stats[0] += 1.0;
+                    sm.stats[1] += epr;
+                    sm.stats[2] += (double)cs;
+                    sm.stats[3] += (double)covsum / (double)fc;
+                    nr = 1;
+                }
+            }
+            p.reward[e] = (float)r;
+            if (p.reward64) p.reward64[e] = r;
+            p.done[e] = (uint8_t)dn;
+            flag = nr && p.auto_reset;
+            p.needs_reset[e] = (nr && !flag) ? 1 : 0;
+        }
+        again = __shfl_sync(FULL, flag, 0) != 0;
+    } else if (fresh && lane == 0) {
+        head->currstep = 0;                                        // :479
+        head->map_idx = map_idx;
+        head->flags = 0;                                           // _robot_pad starts empty (:487)
+        head->episode = head->episode + 1;
+        head->ep_return = 0.0;
+        p.needs_reset[e] = 0;
+    }
+    __syncwarp();
+    if (again) return true;                                        // obs comes from the reset pass
+
+    // ---- observation block: bit rows -> float32, coalesced 128-bit streaming stores ------------
+    float* obs_e = p.obs + (size_t)e * p.obs_env_floats;
+    if (p.vec_ok) {
+        float4* dst = reinterpret_cast<float4*>(obs_e);
+        const int nf4 = p.obs_env_floats >> 2;
+        for (int q = lane; q < nf4; q += 32) {
+            const int k0 = 4 * q;
+            int r0 = fast_div(k0, p.ow_magic);
+            const int b0 = k0 - r0 * ow;
+            uint32_t w = sm.rows[r0] >> b0;
+            int have = ow - b0;
+            while (have < 4) {                                     // rows array is padded with zeros
+                ++r0;
+                w |= sm.rows[r0] << have;
+                have += ow;
+            }
+            __stcs(dst + q, lut[w & 15u]);
+        }
+    } else {
+        for (int k = lane; k < p.obs_env_floats; k += 32) {
+            const int r0 = fast_div(k, p.ow_magic);
+            const int b0 = k - r0 * ow;
+            __stcs(obs_e + k, ((sm.rows[r0] >> b0) & 1u) ? 1.0f : 0.0f);
+        }
+    }
+    return false;
+}
+
+template <bool LIDAR>
+__global__ void __launch_bounds__(MAX_WARPS * 32, 4)
+dec_env_kernel(const DecParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ float4 lut[16];
+    __shared__ int last_flag;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warps = blockDim.x >> 5;
+    const WarpSmem sm = carve(smem_raw + (size_t)warp * p.warp_smem, p);
+
+    if (threadIdx.x < 16) {
+        const uint32_t t = threadIdx.x;
+        lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
+                             (t & 8u) ? 1.0f : 0.0f);
+    }
+    if (lane < MCOV_STATS_LEN) sm.stats[lane] = 0.0;
+    for (int k = lane; k < p.rows_words; k += 32) sm.rows[k] = 0;   // gated layers / padding stay 0
+    __syncthreads();
+
+    const int wg = blockIdx.x * warps + warp, wtot = gridDim.x * warps;
+    const int mode = p.mode;
+    Prefetch nxt;
+    nxt.pos = 0; nxt.act8 = 0; nxt.act64 = 0; nxt.map_idx = 0; nxt.shown = 0;
+    if (mode != MODE_RESET && wg < p.E) nxt = load_prefetch(p, wg, lane);
+    for (int e = wg; e < p.E; e += wtot) {
+        const Prefetch cur = nxt;
+        if (mode != MODE_RESET && e + wtot < p.E) nxt = load_prefetch(p, e + wtot, lane);
+        int m = mode;
+        if (m == MODE_RESET) {
+            int act = 1;
+            if (p.mask) act = p.mask[e];
+            else if (p.mask_from_flags) act = p.needs_reset[e];
+            if (!act) continue;                                    // warp-uniform
+        }
+        while (env_pass<LIDAR>(p, sm, lut, e, m, cur, lane)) m = MODE_RESET;   // fused auto-reset
+    }
+
+    // ---- episode statistics: warp sums -> CTA row -> last CTA folds all rows (single launch) ---
+    if (p.stats_out) {
+        __syncthreads();
+        if (threadIdx.x < MCOV_STATS_LEN) {
+            double s = 0.0;
+            for (int w = 0; w < warps; ++w)
+                s += reinterpret_cast<const double*>(smem_raw + (size_t)w * p.warp_smem)[threadIdx.x];
+            p.stats_partial[(size_t)blockIdx.x * MCOV_STATS_LEN + threadIdx.x] = s;
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) last_flag = (atomicAdd(p.counter, 1u) == gridDim.x - 1) ? 1 : 0;
+        __syncthreads();
+        if (last_flag) {
+            __threadfence();
+            double* red = reinterpret_cast<double*>(smem_raw);      // all warps are done with smem
+            const int k = threadIdx.x & (MCOV_STATS_LEN - 1), r0 = threadIdx.x >> 3, rstep = blockDim.x >> 3;
+            double s = 0.0;
+            for (int r = r0; r < (int)gridDim.x; r += rstep)
+                s += __ldcg(p.stats_partial + (size_t)r * MCOV_STATS_LEN + k);
+            __syncthreads();
+            red[threadIdx.x] = s;
+            __syncthreads();
+            if (threadIdx.x < MCOV_STATS_LEN) {
+                double t = 0.0;
+                for (int r = 0; r < rstep; ++r) t += red[r * MCOV_STATS_LEN + threadIdx.x];
+                p.stats_out[threadIdx.x] = t;
+            }
+            if (threadIdx.x == 0) *p.counter = 0u;
         }
     }
 }
@@ -538,48 +685,62 @@ __global__ void percent_covered_kernel(int E, int N, const unsigned char* hdr, i
     }
 }
 
-inline int pick_lpa(const mcov_config& c) {
-    const int S = 2 * c.sensor_range + 1, ow = 2 * c.egoradius + 1;
-    const bool small = c.num_robots <= 16 && S <= 16 && ow <= 16 && c.sensor_type == MCOV_SENSOR_SQUARE;
-    return small ? 16 : 32;
-}
+struct DecLaunchShape {
+    int warps, grid;
+    size_t warp_smem, smem;
+    int rows_words;
+};
 
-}  // namespace
-
-int dec_grid_size(const mcov_env* env) {
-    const int lpa = pick_lpa(env->cfg);
-    const int threads = env->cfg.num_robots * lpa;
-    const int S = 2 * env->cfg.sensor_range + 1, ow = 2 * env->cfg.egoradius + 1;
-    const size_t smem = dec_smem_bytes(env->cfg.num_robots * env->obs_C * ow * ow, env->cfg.num_robots, S);
-    int per_sm = 2048 / round_up(threads, 32);
-    if (per_sm > 32) per_sm = 32;
-    const int by_smem = (int)((220 * 1024) / (smem + 1024));
+inline DecLaunchShape dec_shape(const mcov_env* env) {
+    const mcov_config& c = env->cfg;
+    const int N = c.num_robots, S = 2 * c.sensor_range + 1, ow = 2 * c.egoradius + 1;
+    DecLaunchShape s;
+    s.rows_words = round_up(N * env->obs_C * ow + 4, 4);
+    const int words = s.rows_words + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 : 2) * N * S + 2 * N;
+    s.warp_smem = (size_t)round_up(MCOV_STATS_LEN * 8 + words * 4, 16);
+    int warps = (int)((200 * 1024) / s.warp_smem);
+    if (warps > MAX_WARPS) warps = MAX_WARPS;
+    if (warps < 1) warps = 1;
+    s.warps = warps;
+    s.smem = s.warp_smem * warps;
+    // the statistics fold reuses the CTA's dynamic smem as blockDim doubles
+    if (s.smem < (size_t)warps * 32 * 8) s.smem = (size_t)warps * 32 * 8;
+    int per_sm = 4;
+    const int by_smem = (int)((220 * 1024) / (s.smem + 1024));
     if (per_sm > by_smem) per_sm = by_smem;
     if (per_sm < 1) per_sm = 1;
     int grid = env->num_sms * per_sm;
-    if (grid > env->cfg.num_envs) grid = env->cfg.num_envs;
-    return grid;
+    const int need = (c.num_envs + warps - 1) / warps;
+    if (grid > need) grid = need;
+    s.grid = grid;
+    return s;
 }
 
+inline uint32_t magic_for(int d) { return (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); }
+
+}  // namespace
+
+int dec_grid_size(const mcov_env* env) { return dec_shape(env).grid; }
+
 cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
-    const int lpa = pick_lpa(env->cfg);
-    const int threads = round_up(p.N * lpa, 32);
-    const size_t smem = dec_smem_bytes(p.obs_env_floats, p.N, p.S);
-    const int grid = dec_grid_size(env);
+    const DecLaunchShape s = dec_shape(env);
+    p.rad = p.ego > p.R ? p.ego : p.R;
+    p.RW = 2 * p.rad + 1;
+    p.rows_words = s.rows_words;
+    p.warp_smem = (int)s.warp_smem;
+    p.ow_magic = magic_for(p.ow);
+    p.rw_magic = magic_for(p.RW);
+    p.s_magic = magic_for(p.S);
+    p.n_magic = magic_for(p.N);
+    const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
     cudaError_t err;
-    if (lpa == 16) {
-        if (smem > 48 * 1024) {
-            err = cudaFuncSetAttribute(dec_env_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (err != cudaSuccess) return err;
-        }
-        dec_env_kernel<16><<<grid, threads, smem, st>>>(p);
-    } else {
-        if (smem > 48 * 1024) {
-            err = cudaFuncSetAttribute(dec_env_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (err != cudaSuccess) return err;
-        }
-        dec_env_kernel<32><<<grid, threads, smem, st>>>(p);
+    if (s.smem > 48 * 1024) {
+        err = lidar ? cudaFuncSetAttribute(dec_env_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem)
+                    : cudaFuncSetAttribute(dec_env_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
+        if (err != cudaSuccess) return err;
     }
+    if (lidar) dec_env_kernel<true><<<s.grid, s.warps * 32, s.smem, st>>>(p);
+    else dec_env_kernel<false><<<s.grid, s.warps * 32, s.smem, st>>>(p);
     env->launches++;
     return cudaGetLastError();
 }

@@ -9,6 +9,7 @@
 namespace mcov {
 
 enum { MODE_STEP = 0, MODE_RESET = 1, MODE_OBSERVE = 2 };
+enum { PH_MOVE = 1, PH_SENSE = 2 };   // step phases (split only for the dist_reward pipeline)
 
 // Parameter block of the DecGridRL kernels (passed by value).
 struct DecParams {
@@ -49,9 +50,18 @@ struct DecParams {
     float* reward;
     double* reward64;
     uint8_t* done;
-    double* stats_partial;    // [gridDim][MCOV_STATS_LEN] or null
+    double* stats_partial;    // [gridDim][MCOV_STATS_LEN] scratch rows
+    double* stats_out;        // [MCOV_STATS_LEN] or null: folded by the last CTA of the launch
+    unsigned int* counter;    // CTA arrival counter for that fold (zero between launches)
     int obs_env_floats;       // N*C*ow*ow
-    int bulk_ok;              // env obs block is a multiple of 16 bytes and obs is 16B aligned
+    int vec_ok;               // env obs block is a multiple of 16 bytes and obs is 16B aligned
+    int phases;               // PH_MOVE | PH_SENSE
+    uint2* move_scratch;      // [E] (collisions, shown mask) handed from a PH_MOVE to a PH_SENSE launch
+    int skip_wipe;            // reset: planes were already zeroed by a memset
+    // launch-derived (filled by launch_dec)
+    int rad, RW;              // rad = max(ego, R), RW = 2*rad+1 rows of the fused band
+    int rows_words, warp_smem;
+    uint32_t ow_magic, rw_magic, s_magic, n_magic;
 };
 
 struct SuperParams {
