@@ -12,17 +12,19 @@
 //   reset                     dec_grid_rl.py:449-531
 //   done / percent_covered    dec_grid_rl.py:533-552
 //
-// Mapping: ONE WARP owns one env per loop iteration (persistent warp-stride loop, up to 8 warps per
-// CTA, 4 CTAs per SM -> 32 envs in flight per SM, no CTA-wide barrier on the path).  Lanes < N hold
-// the robots' poses for the sequential collision-checked moves (shuffle + ballot); afterwards lanes
-// own (robot, window-row) pairs.  All per-robot maps are bit planes in HBM ("strip-major", see
+// Mapping: a GROUP of G lanes (8, 16 or 32 >= numrobot) owns one env per loop iteration, so a warp
+// steps 32/G envs at once (persistent group-stride loop, 256 threads per CTA, 4 CTAs per SM -> up
+// to 128 envs in flight per SM, no CTA-wide barrier on the path).  Lanes < N of a group hold the
+// robots' poses for the sequential collision-checked moves (shuffle + ballot); afterwards lanes own
+// (robot, window-row) pairs.  All per-robot maps are bit planes in HBM ("strip-major", see
 // include/mcov.h); a window row is a <=32-bit field cut from <=2 words with a funnel shift.  The
 // words under the observation window are loaded ONCE and serve both the memory update
 // (free_i/obst_i |= sensor hits) and the observation rows.  Newly covered cells are counted with
 // __popc + warp reductions, no global atomics: every bitmap word has exactly one writer (owner
-// election when footprints overlap).  The float32 observation block of the env is expanded from
-// the bit rows (4 bits -> one float4 through a 16-entry shared-memory table) and stored with
-// coalesced 128-bit streaming stores straight into the torch buffer.  The next env's header, poses
+// election when footprints overlap).  Observation rows are ORed into a per-env bit stream in
+// shared memory (bit k = float k of the env's obs block); the float32 block is expanded from it
+// (4 bits -> one float4 through a 16-entry shared-memory table) and stored with coalesced 128-bit
+// streaming stores straight into the torch buffer.  The next env's header, poses
 // and actions are prefetched into registers while the current env is processed.
 #include "mcov_internal.h"
 
@@ -84,17 +86,36 @@ __device__ void draw_reset(const DecParams& p, int e, uint32_t episode, uint32_t
     for (; placed < p.N; ++placed) posS[placed] = pack_xy(0, 0);
 }
 
+// ---- lane groups: G consecutive lanes (8, 16 or 32) own one env; a warp steps 32/G envs at once.
+// Every warp-level primitive below names only the group's lanes, so groups of one warp may diverge
+// (e.g. one of them re-seeding a finished env) without deadlock.
+template <int G>
+struct Grp {
+    int lane, lg, gbase;
+    unsigned mask;
+    __device__ __forceinline__ explicit Grp(int lane_) : lane(lane_), lg(lane_ & (G - 1)), gbase(lane_ & ~(G - 1)) {
+        mask = G == 32 ? FULL : (((1u << (G & 31)) - 1u) << gbase);
+    }
+    __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(mask, v, src, G); }
+    __device__ __forceinline__ uint32_t ballot(bool pred) const {
+        return (__ballot_sync(mask, pred) >> gbase) & (G == 32 ? FULL : ((1u << (G & 31)) - 1u));
+    }
+    __device__ __forceinline__ bool any(bool pred) const { return __any_sync(mask, pred) != 0; }
+    __device__ __forceinline__ int sum(int v) const { return (int)__reduce_add_sync(mask, v); }
+    __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+};
+
 // Raw (untouched) register copies of the next env's inputs: nothing is computed on them until the
 // env is processed, so the loads stay in flight behind the current env's work.
 struct Prefetch {
-    uint32_t pos;        // lane < N: packed pose
-    uint32_t act8;       // lane < N: per-robot move (U8 format)
+    uint32_t pos;        // lg < N: packed pose
+    uint32_t act8;       // lg < N: per-robot move (U8 format)
     long long act64;     // base-4 joint action (I64 format)
     int map_idx;
     uint32_t shown;
 };
 
-__device__ __forceinline__ Prefetch load_prefetch(const DecParams& p, int e, int lane) {
+__device__ __forceinline__ Prefetch load_prefetch(const DecParams& p, int e, int lg) {
     Prefetch f;
     const unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
     const EnvHead* head = reinterpret_cast<const EnvHead*>(hrec);
@@ -103,71 +124,92 @@ __device__ __forceinline__ Prefetch load_prefetch(const DecParams& p, int e, int
     f.pos = 0;
     f.act8 = 0;
     f.act64 = 0;
-    if (lane < p.N) f.pos = reinterpret_cast<const uint32_t*>(hrec + p.off_pos)[lane];
+    if (lg < p.N) f.pos = reinterpret_cast<const uint32_t*>(hrec + p.off_pos)[lg];
     if (p.mode == MODE_STEP) {
         if (p.act_fmt == MCOV_ACT_I64_BASE4) f.act64 = reinterpret_cast<const long long*>(p.actions)[e];
-        else if (lane < p.N) f.act8 = reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * p.N + lane];
+        else if (lg < p.N) f.act8 = reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * p.N + lg];
     }
     return f;
 }
 
-struct WarpSmem {
-    double* stats;       // [MCOV_STATS_LEN] running sums of this warp (lane 0 only)
-    uint32_t* rows;      // [N*C*ow (+pad)] observation bit rows, flat [robot][channel][row]
-    uint32_t* winF;      // [N*S] sensor-window free hits, window-relative bits
-    uint32_t* winO;      // [N*S] sensor-window obstacle hits
+// per-group shared memory
+struct GroupSmem {
+    double* stats;       // [MCOV_STATS_LEN] running sums of this group (lg 0 only)
+    uint32_t* bits;      // [bits_words] observation bit stream: bit k = float k of the env's obs block
     uint32_t* posF;      // [N] poses after the moves
+    uint32_t* nearM;     // [N] robots whose sensor rows may share a bitmap word with robot i
     int* covS;           // [N] per-robot newly known-free cells of this step
-    uint32_t* wallW;     // [N*S] lidar: truth wall window
+    uint32_t* winF;      // lidar only: [N*S] sensor-window free hits, window-relative bits
+    uint32_t* winO;      //             [N*S] obstacle hits
+    uint32_t* wallW;     //             [N*S] truth wall window
 };
 
-__device__ __forceinline__ WarpSmem carve(unsigned char* base, const DecParams& p) {
-    WarpSmem s;
+__device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams& p) {
+    GroupSmem s;
     s.stats = reinterpret_cast<double*>(base);
-    s.rows = reinterpret_cast<uint32_t*>(base + MCOV_STATS_LEN * 8);
-    s.winF = s.rows + p.rows_words;
+    s.bits = reinterpret_cast<uint32_t*>(base + MCOV_STATS_LEN * 8);
+    s.posF = s.bits + p.bits_words;
+    s.nearM = s.posF + p.N;
+    s.covS = reinterpret_cast<int*>(s.nearM + p.N);
+    s.winF = reinterpret_cast<uint32_t*>(s.covS + p.N);
     s.winO = s.winF + p.N * p.S;
-    s.posF = s.winO + p.N * p.S;
-    s.covS = reinterpret_cast<int*>(s.posF + p.N);
-    s.wallW = reinterpret_cast<uint32_t*>(s.covS + p.N);
+    s.wallW = s.winO + p.N * p.S;
     return s;
 }
 
+// ORs the low `width` bits of `v` into the bit stream at bit offset `off` (shared-memory atomics:
+// neighbouring rows share words).
+__device__ __forceinline__ void stream_or(uint32_t* bits, int off, uint32_t v, int width) {
+    if (v == 0) return;
+    const int w = off >> 5, sh = off & 31;
+    atomicOr(bits + w, v << sh);
+    if (sh + width > 32) atomicOr(bits + w + 1, v >> (32 - sh));
+}
+
+// Sensor-frame helpers.  A robot at (xj, yj) with range R touches, in map row x (|x - xj| <= R),
+// the cells y in [yj-R, yj+R]; `ymask_in_strip` is that interval cut to absolute strip s.
+__device__ __forceinline__ uint32_t ymask_in_strip(int yj, int R, int S, int s) {
+    const int y0 = yj - R, s0 = y0 >> 5;
+    const uint64_t m = (uint64_t)low_mask(S) << (y0 & 31);
+    return s == s0 ? (uint32_t)m : (s == s0 + 1 ? (uint32_t)(m >> 32) : 0u);
+}
+
 // One pass over env e in `mode`.  Returns true when a finished env must be re-seeded in place by a
-// second (MODE_RESET) pass of the same warp (fused auto-reset).
-template <bool LIDAR>
-__device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm, const float4* lut,
+// second (MODE_RESET) pass of the same lane group (fused auto-reset).
+template <int G, bool LIDAR>
+__device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut,
                                          const int e, const int mode, const Prefetch& cur,
-                                         const int lane) {
+                                         const Grp<G>& g) {
     const int N = p.N, S = p.S, R = p.R, W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips;
     const int PW = p.g.PW;
     const int ow = p.ow, ego = p.ego, C = p.C, rad = p.rad, RW = p.RW;
+    const int lg = g.lg;
 
     unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
     EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
     uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
     int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
-    uint32_t* hadj = reinterpret_cast<uint32_t*>(hrec + p.off_adj);
     uint2* fo_e = p.fo + (size_t)e * N * PW;
     uint32_t* vis = p.visited + (size_t)e * PW;
 
+    g.sync();                                    // previous pass has finished reading sm.bits
     const bool fresh = (mode == MODE_RESET);
     int map_idx;
     uint32_t shown, myv;
     if (fresh) {
         int mi = 0;
-        if (lane == 0) draw_reset(p, e, head->episode, sm.posF, &mi);
-        map_idx = __shfl_sync(FULL, mi, 0);
+        if (lg == 0) draw_reset(p, e, head->episode, sm.posF, &mi);
+        map_idx = g.shfl(mi, 0);
         if (!p.skip_wipe) {
             // wipe this env's planes (dec_grid_rl.py:505-514) with 128-bit stores
             uint4* z = reinterpret_cast<uint4*>(fo_e);
             const int n16 = N * (PW / 2);
-            for (int k = lane; k < n16; k += 32) z[k] = make_uint4(0, 0, 0, 0);
+            for (int k = lg; k < n16; k += G) z[k] = make_uint4(0, 0, 0, 0);
             uint4* zv = reinterpret_cast<uint4*>(vis);
-            for (int k = lane; k < PW / 4; k += 32) zv[k] = make_uint4(0, 0, 0, 0);
+            for (int k = lg; k < PW / 4; k += G) zv[k] = make_uint4(0, 0, 0, 0);
         }
-        __syncwarp();
-        myv = lane < N ? sm.posF[lane] : 0u;
+        g.sync();
+        myv = lg < N ? sm.posF[lg] : 0u;
         shown = 0;
     } else {
         map_idx = cur.map_idx;
@@ -180,14 +222,14 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
     // early loads for the bookkeeping at the end of the pass (kept in flight until then)
     int cs0 = 0, fc = 1;
     double th = 0.0, epr0 = 0.0;
-    if (mode == MODE_STEP && lane == 0) {
+    if (mode == MODE_STEP && lg == 0) {
         cs0 = head->currstep;
         th = head->done_thresh;
         epr0 = head->ep_return;
         fc = __ldg(p.free_counts + map_idx);
     }
     int cov_old = 0;
-    if (mode == MODE_STEP && lane < N) cov_old = hcov[lane];
+    if (mode == MODE_STEP && lg < N) cov_old = hcov[lg];
 
     int px = unpack_x(myv), py = unpack_y(myv);
     int ncoll = 0;
@@ -197,7 +239,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
         int u;
         if (p.act_fmt == MCOV_ACT_I64_BASE4) {
             sentinel = (cur.act64 == -1);
-            u = (int)((cur.act64 >> (2 * (lane & 31))) & 3);
+            u = (int)((cur.act64 >> (2 * lg)) & 3);
         } else {
             u = (int)(cur.act8 & 3u);
         }
@@ -207,20 +249,22 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
             const int tx = px + (u == 0) - (u == 2);
             const int ty = py + (u == 1) - (u == 3);
             int blocked0 = 1;
-            if (lane < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
+            if (lg < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
+            const uint32_t tv = pack_xy(tx, ty);
+            uint32_t pv = myv;
             for (int k = 0; k < N; ++k) {
-                const int txk = __shfl_sync(FULL, tx, k);
-                const int tyk = __shfl_sync(FULL, ty, k);
-                const int blk = __shfl_sync(FULL, blocked0, k);
-                const bool hit = (lane < N) && px == txk && py == tyk;
-                const uint32_t b = __ballot_sync(FULL, hit);
+                const uint32_t tvk = (uint32_t)g.shfl((int)tv, k);
+                const int blk = g.shfl(blocked0, k);
+                const uint32_t b = g.ballot((lg < N) && pv == tvk);
                 if (!blk && b == 0) {
-                    if (lane == k) { px = txk; py = tyk; }
+                    if (lg == k) pv = tvk;
                     shown |= 1u << k;
                 } else {
                     ++ncoll;
                 }
             }
+            px = unpack_x(pv);
+            py = unpack_y(pv);
         } else if (!sentinel) {
             // moves were resolved by an earlier PH_MOVE launch (dist_reward pipeline)
             const uint2 ms = p.move_scratch[e];
@@ -228,60 +272,48 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
             shown = ms.y;
         }
     }
-    // publish poses for cross-robot lookups and persist them
+    // publish poses for cross-robot lookups and persist them; clear the per-pass scratch
     const uint32_t newv = pack_xy(px, py);
-    if (lane < N) {
-        sm.posF[lane] = newv;
-        sm.covS[lane] = 0;
-        if (mode != MODE_OBSERVE && (fresh || newv != myv)) hpos[lane] = newv;
+    if (lg < N) {
+        sm.posF[lg] = newv;
+        sm.covS[lg] = 0;
+        sm.nearM[lg] = 0;
+        if (mode != MODE_OBSERVE && (fresh || newv != myv)) hpos[lg] = newv;
     }
+    for (int k = lg; k < p.bits_words; k += G) sm.bits[k] = 0;
 
     // ---- communication graph (dec_grid_rl.py:374-391): Chebyshev ball, diagonal included ------
     if (mode != MODE_OBSERVE && (p.comm_radius > 0 || fresh)) {
-        uint32_t myadj = 1u << lane;
+        uint32_t myadj = 1u << lg;
         if (p.comm_radius > 0) {
             for (int i = 0; i < N; ++i) {
-                const int xi = __shfl_sync(FULL, px, i), yi = __shfl_sync(FULL, py, i);
-                const bool link = (lane < N) && max(abs(px - xi), abs(py - yi)) <= p.comm_radius;
-                const uint32_t b = __ballot_sync(FULL, link);
-                if (lane == i) myadj = b;
+                const int xi = g.shfl(px, i), yi = g.shfl(py, i);
+                const uint32_t b = g.ballot((lg < N) && max(abs(px - xi), abs(py - yi)) <= p.comm_radius);
+                if (lg == i) myadj = b;
             }
         }
-        if (lane < N) hadj[lane] = myadj;
+        if (lg < N) reinterpret_cast<uint32_t*>(hrec + p.off_adj)[lg] = myadj;
     }
     if (mode == MODE_STEP && !(p.phases & PH_SENSE)) {
-        if (lane == 0) p.move_scratch[e] = make_uint2((uint32_t)ncoll, shown);
+        if (lg == 0) p.move_scratch[e] = make_uint2((uint32_t)ncoll, shown);
         return false;
     }
-    __syncwarp();
+    g.sync();
 
     const bool do_sense = fresh || (mode == MODE_STEP && !sentinel);
-    bool near_other = false;
     if (do_sense) {
-        // can another robot's sensor rows share a bitmap word with mine?
-        if (lane < N)
-            for (int j = 0; j < N; ++j) {
-                const uint32_t pj = sm.posF[j];
-                near_other |= (j != lane) && abs(px - unpack_x(pj)) <= 2 * R && abs(py - unpack_y(pj)) < S + 32;
-            }
-        if (!LIDAR) {
-            // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
-            for (int idx = lane; idx < N * S; idx += 32) {
-                const int i = fast_div(idx, p.s_magic), r = idx - i * S;
-                const uint32_t pi = sm.posF[i];
-                const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
-                uint32_t f = 0, o = 0;
-                if (x >= 0 && x < W) {
-                    o = read_window(wall, Wp, strips, x, y0, S);
-                    if (p.single_tool) f = (r == R) ? (1u << R) : 0u;       // dec_grid_rl.py:233-234
-                    else f = read_window(tpos, Wp, strips, x, y0, S);
-                }
-                sm.winF[idx] = f;
-                sm.winO[idx] = o;
-            }
-        } else {
+        // which robots' sensor rows can share a bitmap word with robot i's?  (one lane per pair)
+        for (int idx = lg; idx < N * N; idx += G) {
+            const int i = fast_div(idx, p.n_magic), j = idx - i * N;
+            const uint32_t pi = sm.posF[i], pj = sm.posF[j];
+            const int yi = unpack_y(pi), yj = unpack_y(pj);
+            const bool nr = (i != j) && abs(unpack_x(pi) - unpack_x(pj)) <= 2 * R &&
+                            max((yi - R) >> 5, (yj - R) >> 5) <= min((yi + R) >> 5, (yj + R) >> 5);
+            if (nr) atomicOr(&sm.nearM[i], 1u << j);
+        }
+        if (LIDAR) {
             // lidar.py:16-65 — stage the truth wall window, then march beams in float64
-            for (int idx = lane; idx < N * S; idx += 32) {
+            for (int idx = lg; idx < N * S; idx += G) {
                 const int i = fast_div(idx, p.s_magic), r = idx - i * S;
                 const uint32_t pi = sm.posF[i];
                 const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
@@ -289,9 +321,9 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
                 sm.winF[idx] = 0;
                 sm.winO[idx] = 0;
             }
-            __syncwarp();
+            g.sync();
             const double rng = (double)R;
-            for (int idx = lane; idx < N * p.n_lasers; idx += 32) {
+            for (int idx = lg; idx < N * p.n_lasers; idx += G) {
                 const int i = idx / p.n_lasers, l = idx - i * p.n_lasers;
                 const uint32_t pi = sm.posF[i];
                 const int xi = unpack_x(pi), yi = unpack_y(pi);
@@ -318,151 +350,149 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
                 }
             }
             if (p.single_tool) {
-                __syncwarp();
-                for (int idx = lane; idx < N * S; idx += 32) {
+                g.sync();
+                for (int idx = lg; idx < N * S; idx += G) {
                     const int i = fast_div(idx, p.s_magic), r = idx - i * S;
-                    sm.winF[idx] = (r == R) ? (1u << R) : 0u;
+                    sm.winF[idx] = (r == R) ? (1u << R) : 0u;      // dec_grid_rl.py:233-234
                 }
             }
         }
+        g.sync();
     }
-    const bool overlap = __any_sync(FULL, near_other);      // also orders winF/winO/posF for the warp
 
     // ---- fused memory update + observation rows ---------------------------------------------
     // Lane slot = (robot i, row a2 of the (2*rad+1)-row band around it), rad = max(ego, R).  The
     // <=2 interleaved {free_i, obst_i} words under the band row are loaded once; rows inside the
-    // sensor range get the hits ORed in and written back; rows inside the egocentric window
-    // produce the observation bit rows.  All loads of both slots are issued before any store.
+    // sensor range get the hits ORed in and written back; rows inside the egocentric window are
+    // ORed into the observation bit stream.
     int cnt = 0;
     const int total = N * RW;
     const uint32_t wm_ow = low_mask(ow);
-    for (int base = 0; base < total; base += 64) {
-        uint2 lo[2], hi[2];
-        uint32_t vlo[2], vhi[2];
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            const int idx = base + 32 * u + lane;
-            lo[u] = make_uint2(0, 0);
-            hi[u] = make_uint2(0, 0);
-            vlo[u] = 0;
-            vhi[u] = 0;
-            if (idx < total && !fresh) {
-                const int i = fast_div(idx, p.rw_magic), a2 = idx - i * RW;
-                const uint32_t pi = sm.posF[i];
-                const int xi = unpack_x(pi), yi = unpack_y(pi);
-                const int x = xi - rad + a2;
-                if (x >= 0 && x < W) {
-                    const int y0r = yi - rad, s0 = y0r >> 5;
-                    const bool in0 = s0 >= 0 && s0 < strips;
-                    const bool in1 = ((y0r & 31) + RW > 32) && s0 + 1 >= 0 && s0 + 1 < strips;
-                    const uint2* fo_i = fo_e + (size_t)i * PW;
-                    const int w0 = s0 * Wp + x;
-                    if (in0) lo[u] = fo_i[w0];
-                    if (in1) hi[u] = fo_i[w0 + Wp];
-                    if (do_sense && abs(x - xi) <= R) {
-                        const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
-                        if (in0 && s0 >= ys0) vlo[u] = vis[w0];
-                        if (in1 && s0 + 1 <= ys1) vhi[u] = vis[w0 + Wp];
-                    }
-                }
-            }
+    const int ow2 = ow * ow;
+    for (int idx = lg; idx < total; idx += G) {
+        const int i = fast_div(idx, p.rw_magic), a2 = idx - i * RW;
+        const uint32_t pi = sm.posF[i];
+        const int xi = unpack_x(pi), yi = unpack_y(pi);
+        const int x = xi - rad + a2;
+        const bool inx = x >= 0 && x < W;
+        const int y0r = yi - rad, s0 = y0r >> 5, sh = y0r & 31;
+        const bool in0 = inx && s0 >= 0 && s0 < strips;
+        const bool in1 = inx && (sh + RW > 32) && s0 + 1 >= 0 && s0 + 1 < strips;
+        const int w0 = s0 * Wp + x;
+        uint2* fo_i = fo_e + (size_t)i * PW;
+        const bool sens = do_sense && inx && abs(x - xi) <= R;
+
+        uint2 lo = make_uint2(0, 0), hi = make_uint2(0, 0);
+        if (!fresh) {
+            if (in0) lo = fo_i[w0];
+            if (in1) hi = fo_i[w0 + Wp];
         }
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            const int idx = base + 32 * u + lane;
-            if (idx >= total) continue;
-            const int i = fast_div(idx, p.rw_magic), a2 = idx - i * RW;
-            const uint32_t pi = sm.posF[i];
-            const int xi = unpack_x(pi), yi = unpack_y(pi);
-            const int x = xi - rad + a2;
-            const bool inx = x >= 0 && x < W;
-            const int y0r = yi - rad, s0 = y0r >> 5, sh = y0r & 31;
-            uint2 nlo = lo[u], nhi = hi[u];
-            if (inx && do_sense && abs(x - xi) <= R) {
-                const bool in0 = s0 >= 0 && s0 < strips;
-                const bool in1 = (sh + RW > 32) && s0 + 1 >= 0 && s0 + 1 < strips;
+        uint2 nlo = lo, nhi = hi;
+        if (sens) {
+            const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
+            const bool t0 = in0 && s0 >= ys0, t1 = in1 && s0 + 1 <= ys1;
+            uint32_t vlo = 0, vhi = 0;
+            if (!fresh) {
+                if (t0) vlo = vis[w0];
+                if (t1) vhi = vis[w0 + Wp];
+            }
+            uint32_t f0 = 0, f1 = 0, o0 = 0, o1 = 0;
+            if (!LIDAR) {
+                // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
+                const uint64_t m64 = (uint64_t)low_mask(S) << (sh + rad - R);
+                const uint32_t m0 = (uint32_t)m64, m1 = (uint32_t)(m64 >> 32);
+                if (in0) { o0 = __ldg(wall + w0) & m0; f0 = __ldg(tpos + w0) & m0; }
+                if (in1) { o1 = __ldg(wall + w0 + Wp) & m1; f1 = __ldg(tpos + w0 + Wp) & m1; }
+                if (p.single_tool) {                               // dec_grid_rl.py:233-234
+                    const uint64_t c64 = (x == xi) ? (1ull << (sh + rad)) : 0ull;
+                    f0 = in0 ? (uint32_t)c64 : 0u;
+                    f1 = in1 ? (uint32_t)(c64 >> 32) : 0u;
+                }
+            } else {
                 const int r = x - xi + R;
-                uint32_t f0, f1, o0, o1;
                 split_words(sm.winF[i * S + r] << (rad - R), y0r, f0, f1);
                 split_words(sm.winO[i * S + r] << (rad - R), y0r, o0, o1);
-                uint2* fo_i = fo_e + (size_t)i * PW;
-                const int w0 = s0 * Wp + x;
-                // per-robot memory: free_i |= hits, obst_i |= hits  (dec_grid_rl.py:231-236)
-                nlo = make_uint2(lo[u].x | f0, lo[u].y | o0);
-                nhi = make_uint2(hi[u].x | f1, hi[u].y | o1);
-                const int cn = __popc(f0 & ~lo[u].x) + __popc(f1 & ~hi[u].x);
-                if (in0 && (nlo.x != lo[u].x || nlo.y != lo[u].y)) fo_i[w0] = nlo;
-                if (in1 && (nhi.x != hi[u].x || nhi.y != hi[u].y)) fo_i[w0 + Wp] = nhi;
-                if (cn) atomicAdd(&sm.covS[i], cn);                 // shared-memory atomic
-                // union "visited" plane: exactly one writer per word (dec_grid_rl.py:243-256)
-                const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
+                if (!in0) { f0 = 0; o0 = 0; }
+                if (!in1) { f1 = 0; o1 = 0; }
+            }
+            // per-robot memory: free_i |= hits, obst_i |= hits  (dec_grid_rl.py:231-236)
+            nlo = make_uint2(lo.x | f0, lo.y | o0);
+            nhi = make_uint2(hi.x | f1, hi.y | o1);
+            const int cn = __popc(f0 & ~lo.x) + __popc(f1 & ~hi.x);
+            if (in0 && (nlo.x != lo.x || nlo.y != lo.y)) fo_i[w0] = nlo;
+            if (in1 && (nhi.x != hi.x || nhi.y != hi.y)) fo_i[w0 + Wp] = nhi;
+            if (cn) atomicAdd(&sm.covS[i], cn);                     // shared-memory atomic
+            // union "visited" plane: exactly one writer per word (dec_grid_rl.py:243-256)
+            const uint32_t nm = sm.nearM[i];
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const int s = s0 + k;
-                    if (!(k == 0 ? in0 : in1) || s < ys0 || s > ys1) continue;
-                    uint32_t comb = k == 0 ? f0 : f1;
-                    bool owner = true;
-                    if (overlap) {
-                        for (int j = 0; j < N; ++j) {
-                            if (j == i) continue;
-                            const uint32_t pj = sm.posF[j];
-                            const int rj = x - (unpack_x(pj) - R);
-                            if (rj < 0 || rj >= S) continue;
-                            const int y0j = unpack_y(pj) - R;
-                            const int s0j = y0j >> 5;
-                            uint32_t jl, jh;
-                            split_words(sm.winF[j * S + rj], y0j, jl, jh);
-                            if (s == s0j) { comb |= jl; owner &= (j > i); }
-                            else if (s == s0j + 1 && (y0j & 31) + S > 32) { comb |= jh; owner &= (j > i); }
-                        }
-                    }
-                    if (owner) {
-                        const uint32_t vold = k == 0 ? vlo[u] : vhi[u];
-                        const uint32_t nb = comb & ~vold;
-                        cnt += __popc(nb);
-                        if (nb) vis[w0 + k * Wp] = vold | comb;
+            for (int k = 0; k < 2; ++k) {
+                if (!(k == 0 ? t0 : t1)) continue;
+                const int s = s0 + k;
+                uint32_t comb = k == 0 ? f0 : f1;
+                bool owner = true;
+                for (uint32_t mm = nm; mm; mm &= mm - 1) {          // rare: footprints overlap
+                    const int j = __ffs(mm) - 1;
+                    const uint32_t pj = sm.posF[j];
+                    const int xj = unpack_x(pj), yj = unpack_y(pj);
+                    if (abs(x - xj) > R) continue;
+                    const int y0j = yj - R, s0j = y0j >> 5;
+                    if (s < s0j || s > ((yj + R) >> 5)) continue;
+                    owner &= (j > i);
+                    if (LIDAR) {
+                        uint32_t jl, jh;
+                        split_words(sm.winF[j * S + (x - xj + R)], y0j, jl, jh);
+                        comb |= (s == s0j) ? jl : jh;
+                    } else if (p.single_tool) {
+                        comb |= (x == xj && (yj >> 5) == s) ? (1u << (yj & 31)) : 0u;
+                    } else {
+                        comb |= __ldg(tpos + w0 + k * Wp) & ymask_in_strip(yj, R, S, s);
                     }
                 }
-            }
-            // egocentric observation rows (dec_grid_rl.py:334-347); layer 0 is filled below
-            const int a = x - (xi - ego);
-            if (a >= 0 && a < ow) {
-                const uint32_t bF = (__funnelshift_r(nlo.x, nhi.x, sh) >> (rad - ego)) & wm_ow;
-                const uint32_t bO = (__funnelshift_r(nlo.y, nhi.y, sh) >> (rad - ego)) & wm_ow;
-                uint32_t* rw = sm.rows + (size_t)(i * C) * ow + a;
-                rw[0] = 0;
-                rw[ow] = bF;
-                rw[2 * ow] = bO;
+                if (owner) {
+                    const uint32_t vold = k == 0 ? vlo : vhi;
+                    const uint32_t nb = comb & ~vold;
+                    cnt += __popc(nb);
+                    if (nb) vis[w0 + k * Wp] = vold | comb;
+                }
             }
         }
+        // egocentric observation rows (dec_grid_rl.py:334-347): layers 1 (free_i) and 2 (obst_i)
+        const int a = a2 - (rad - ego);
+        if (a >= 0 && a < ow) {
+            const uint32_t bF = (__funnelshift_r(nlo.x, nhi.x, sh) >> (rad - ego)) & wm_ow;
+            const uint32_t bO = (__funnelshift_r(nlo.y, nhi.y, sh) >> (rad - ego)) & wm_ow;
+            const int off = ((i * C + 1) * ow + a) * ow;
+            stream_or(sm.bits, off, bF, ow);
+            stream_or(sm.bits, off + ow2, bO, ow);
+        }
     }
-    __syncwarp();
     // layer 0 shows every robot that has moved at least once (quirk A.3.4): one lane per
     // (viewer i, shown robot j) pair
-    for (int idx = lane; idx < N * N; idx += 32) {
+    for (int idx = lg; idx < N * N; idx += G) {
         const int i = fast_div(idx, p.n_magic), j = idx - i * N;
         if (!((shown >> j) & 1u)) continue;
         const uint32_t pi = sm.posF[i], pj = sm.posF[j];
         const int a = unpack_x(pj) - (unpack_x(pi) - ego), b = unpack_y(pj) - (unpack_y(pi) - ego);
-        if (a >= 0 && a < ow && b >= 0 && b < ow) atomicOr(&sm.rows[(size_t)(i * C) * ow + a], 1u << b);
+        if (a >= 0 && a < ow && b >= 0 && b < ow) stream_or(sm.bits, (i * C * ow + a) * ow + b, 1u, 1);
     }
+    g.sync();
 
     // ---- reward / termination bookkeeping ------------------------------------------------------
-    cnt = __reduce_add_sync(FULL, cnt);
+    cnt = g.sum(cnt);
     int covsum = 0;
     if (mode != MODE_OBSERVE) {
         int c = 0;
-        if (lane < N) {
-            const int dn = sm.covS[lane];
+        if (lg < N) {
+            const int dn = sm.covS[lg];
             c = cov_old + dn;
-            if (fresh || dn != 0) hcov[lane] = c;                  // per-robot known-free count
+            if (fresh || dn != 0) hcov[lg] = c;                    // per-robot known-free count
         }
-        covsum = __reduce_add_sync(FULL, c);
+        covsum = g.sum(c);
     }
     bool again = false;
     if (mode == MODE_STEP) {
         int flag = 0;
-        if (lane == 0) {
+        if (lg == 0) {
             double r = 0.0;
             int dn = 0, nr = 0;
             if (sentinel) {
@@ -502,8 +532,8 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
             flag = nr && p.auto_reset;
             p.needs_reset[e] = (nr && !flag) ? 1 : 0;
         }
-        again = __shfl_sync(FULL, flag, 0) != 0;
-    } else if (fresh && lane == 0) {
+        again = g.shfl(flag, 0) != 0;
+    } else if (fresh && lg == 0) {
         head->currstep = 0;                                        // :479
         head->map_idx = map_idx;
         head->flags = 0;                                           // _robot_pad starts empty (:487)
@@ -511,81 +541,68 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const WarpSmem& sm,
         head->ep_return = 0.0;
         p.needs_reset[e] = 0;
     }
-    __syncwarp();
     if (again) return true;                                        // obs comes from the reset pass
 
-    // ---- observation block: bit rows -> float32, coalesced 128-bit streaming stores ------------
+    // ---- observation block: bit stream -> float32, coalesced 128-bit streaming stores ----------
     float* obs_e = p.obs + (size_t)e * p.obs_env_floats;
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
         const int nf4 = p.obs_env_floats >> 2;
-        for (int q = lane; q < nf4; q += 32) {
-            const int k0 = 4 * q;
-            int r0 = fast_div(k0, p.ow_magic);
-            const int b0 = k0 - r0 * ow;
-            uint32_t w = sm.rows[r0] >> b0;
-            int have = ow - b0;
-            while (have < 4) {                                     // rows array is padded with zeros
-                ++r0;
-                w |= sm.rows[r0] << have;
-                have += ow;
-            }
+        for (int q = lg; q < nf4; q += G) {
+            const uint32_t w = sm.bits[q >> 3] >> ((q & 7) * 4);
             __stcs(dst + q, lut[w & 15u]);
         }
     } else {
-        for (int k = lane; k < p.obs_env_floats; k += 32) {
-            const int r0 = fast_div(k, p.ow_magic);
-            const int b0 = k - r0 * ow;
-            __stcs(obs_e + k, ((sm.rows[r0] >> b0) & 1u) ? 1.0f : 0.0f);
-        }
+        for (int k = lg; k < p.obs_env_floats; k += G)
+            __stcs(obs_e + k, ((sm.bits[k >> 5] >> (k & 31)) & 1u) ? 1.0f : 0.0f);
     }
     return false;
 }
 
-template <bool LIDAR>
+template <int G, bool LIDAR>
 __global__ void __launch_bounds__(MAX_WARPS * 32, 4)
 dec_env_kernel(const DecParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ float4 lut[16];
     __shared__ int last_flag;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int warps = blockDim.x >> 5;
-    const WarpSmem sm = carve(smem_raw + (size_t)warp * p.warp_smem, p);
+    const Grp<G> g(threadIdx.x & 31);
+    const int gpc = blockDim.x / G;                       // lane groups (= envs in flight) per CTA
+    const int gi = threadIdx.x / G;
+    const GroupSmem sm = carve(smem_raw + (size_t)gi * p.grp_smem, p);
 
     if (threadIdx.x < 16) {
         const uint32_t t = threadIdx.x;
         lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
                              (t & 8u) ? 1.0f : 0.0f);
     }
-    if (lane < MCOV_STATS_LEN) sm.stats[lane] = 0.0;
-    for (int k = lane; k < p.rows_words; k += 32) sm.rows[k] = 0;   // gated layers / padding stay 0
+    if (g.lg < MCOV_STATS_LEN) sm.stats[g.lg] = 0.0;
     __syncthreads();
 
-    const int wg = blockIdx.x * warps + warp, wtot = gridDim.x * warps;
+    const int gg = blockIdx.x * gpc + gi, gtot = gridDim.x * gpc;
     const int mode = p.mode;
     Prefetch nxt;
     nxt.pos = 0; nxt.act8 = 0; nxt.act64 = 0; nxt.map_idx = 0; nxt.shown = 0;
-    if (mode != MODE_RESET && wg < p.E) nxt = load_prefetch(p, wg, lane);
-    for (int e = wg; e < p.E; e += wtot) {
+    if (mode != MODE_RESET && gg < p.E) nxt = load_prefetch(p, gg, g.lg);
+    for (int e = gg; e < p.E; e += gtot) {
         const Prefetch cur = nxt;
-        if (mode != MODE_RESET && e + wtot < p.E) nxt = load_prefetch(p, e + wtot, lane);
+        if (mode != MODE_RESET && e + gtot < p.E) nxt = load_prefetch(p, e + gtot, g.lg);
         int m = mode;
         if (m == MODE_RESET) {
             int act = 1;
             if (p.mask) act = p.mask[e];
             else if (p.mask_from_flags) act = p.needs_reset[e];
-            if (!act) continue;                                    // warp-uniform
+            if (!act) continue;                                    // group-uniform
         }
-        while (env_pass<LIDAR>(p, sm, lut, e, m, cur, lane)) m = MODE_RESET;   // fused auto-reset
+        while (env_pass<G, LIDAR>(p, sm, lut, e, m, cur, g)) m = MODE_RESET;   // fused auto-reset
     }
 
-    // ---- episode statistics: warp sums -> CTA row -> last CTA folds all rows (single launch) ---
+    // ---- episode statistics: group sums -> CTA row -> last CTA folds all rows (single launch) --
     if (p.stats_out) {
         __syncthreads();
         if (threadIdx.x < MCOV_STATS_LEN) {
             double s = 0.0;
-            for (int w = 0; w < warps; ++w)
-                s += reinterpret_cast<const double*>(smem_raw + (size_t)w * p.warp_smem)[threadIdx.x];
+            for (int w = 0; w < gpc; ++w)
+                s += reinterpret_cast<const double*>(smem_raw + (size_t)w * p.grp_smem)[threadIdx.x];
             p.stats_partial[(size_t)blockIdx.x * MCOV_STATS_LEN + threadIdx.x] = s;
         }
         __threadfence();
@@ -594,7 +611,7 @@ dec_env_kernel(const DecParams p) {
         __syncthreads();
         if (last_flag) {
             __threadfence();
-            double* red = reinterpret_cast<double*>(smem_raw);      // all warps are done with smem
+            double* red = reinterpret_cast<double*>(smem_raw);      // all groups are done with smem
             const int k = threadIdx.x & (MCOV_STATS_LEN - 1), r0 = threadIdx.x >> 3, rstep = blockDim.x >> 3;
             double s = 0.0;
             for (int r = r0; r < (int)gridDim.x; r += rstep)
@@ -686,37 +703,64 @@ __global__ void percent_covered_kernel(int E, int N, const unsigned char* hdr, i
 }
 
 struct DecLaunchShape {
-    int warps, grid;
-    size_t warp_smem, smem;
-    int rows_words;
+    int G, threads, grid;
+    size_t grp_smem, smem;
+    int bits_words;
 };
+
+inline int pick_group(const mcov_config& c) {
+    // lanes per env: at least the robots (poses live in lanes), 8 otherwise so that the one-lane
+    // phases (moves, bookkeeping) are shared by 4 envs per warp
+    if (c.num_robots > 16) return 32;
+    if (c.num_robots > 8) return 16;
+    return 8;
+}
 
 inline DecLaunchShape dec_shape(const mcov_env* env) {
     const mcov_config& c = env->cfg;
     const int N = c.num_robots, S = 2 * c.sensor_range + 1, ow = 2 * c.egoradius + 1;
     DecLaunchShape s;
-    s.rows_words = round_up(N * env->obs_C * ow + 4, 4);
-    const int words = s.rows_words + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 : 2) * N * S + 2 * N;
-    s.warp_smem = (size_t)round_up(MCOV_STATS_LEN * 8 + words * 4, 16);
-    int warps = (int)((200 * 1024) / s.warp_smem);
-    if (warps > MAX_WARPS) warps = MAX_WARPS;
-    if (warps < 1) warps = 1;
-    s.warps = warps;
-    s.smem = s.warp_smem * warps;
+    s.G = pick_group(c);
+    s.bits_words = (N * env->obs_C * ow * ow + 31) / 32 + 1;
+    int words = s.bits_words + 3 * N + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 * N * S : 0);
+    words = round_up(words, 2);
+    // stagger the groups of one warp over the 32 banks: stride = multiple of 32 words + G
+    int stride_words = MCOV_STATS_LEN * 2 + words;
+    if (s.G < 32) stride_words = round_up(stride_words, 32) + s.G;
+    s.grp_smem = (size_t)stride_words * 4;
+    int groups = MAX_WARPS * 32 / s.G;
+    const int cap = (int)((200 * 1024) / s.grp_smem);
+    if (groups > cap) groups = cap;
+    const int per_warp = 32 / s.G;
+    groups = groups / per_warp * per_warp;
+    if (groups < per_warp) groups = per_warp;
+    s.threads = groups * s.G;
+    s.smem = s.grp_smem * groups;
     // the statistics fold reuses the CTA's dynamic smem as blockDim doubles
-    if (s.smem < (size_t)warps * 32 * 8) s.smem = (size_t)warps * 32 * 8;
+    if (s.smem < (size_t)s.threads * 8) s.smem = (size_t)s.threads * 8;
     int per_sm = 4;
     const int by_smem = (int)((220 * 1024) / (s.smem + 1024));
     if (per_sm > by_smem) per_sm = by_smem;
     if (per_sm < 1) per_sm = 1;
     int grid = env->num_sms * per_sm;
-    const int need = (c.num_envs + warps - 1) / warps;
+    const int need = (c.num_envs + groups - 1) / groups;
     if (grid > need) grid = need;
     s.grid = grid;
     return s;
 }
 
 inline uint32_t magic_for(int d) { return (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); }
+
+template <int G, bool LIDAR>
+cudaError_t launch_dec_t(const DecLaunchShape& s, const DecParams& p, cudaStream_t st) {
+    if (s.smem > 48 * 1024) {
+        cudaError_t err = cudaFuncSetAttribute(dec_env_kernel<G, LIDAR>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
+        if (err != cudaSuccess) return err;
+    }
+    dec_env_kernel<G, LIDAR><<<s.grid, s.threads, s.smem, st>>>(p);
+    return cudaGetLastError();
+}
 
 }  // namespace
 
@@ -726,23 +770,18 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     const DecLaunchShape s = dec_shape(env);
     p.rad = p.ego > p.R ? p.ego : p.R;
     p.RW = 2 * p.rad + 1;
-    p.rows_words = s.rows_words;
-    p.warp_smem = (int)s.warp_smem;
-    p.ow_magic = magic_for(p.ow);
+    p.bits_words = s.bits_words;
+    p.grp_smem = (int)s.grp_smem;
     p.rw_magic = magic_for(p.RW);
     p.s_magic = magic_for(p.S);
     p.n_magic = magic_for(p.N);
     const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
     cudaError_t err;
-    if (s.smem > 48 * 1024) {
-        err = lidar ? cudaFuncSetAttribute(dec_env_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem)
-                    : cudaFuncSetAttribute(dec_env_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
-        if (err != cudaSuccess) return err;
-    }
-    if (lidar) dec_env_kernel<true><<<s.grid, s.warps * 32, s.smem, st>>>(p);
-    else dec_env_kernel<false><<<s.grid, s.warps * 32, s.smem, st>>>(p);
+    if (s.G == 8) err = lidar ? launch_dec_t<8, true>(s, p, st) : launch_dec_t<8, false>(s, p, st);
+    else if (s.G == 16) err = lidar ? launch_dec_t<16, true>(s, p, st) : launch_dec_t<16, false>(s, p, st);
+    else err = lidar ? launch_dec_t<32, true>(s, p, st) : launch_dec_t<32, false>(s, p, st);
     env->launches++;
-    return cudaGetLastError();
+    return err;
 }
 
 cudaError_t launch_dec_share(mcov_env* env, cudaStream_t st) {

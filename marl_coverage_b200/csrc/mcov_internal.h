@@ -60,8 +60,8 @@ struct DecParams {
     int skip_wipe;            // reset: planes were already zeroed by a memset
     // launch-derived (filled by launch_dec)
     int rad, RW;              // rad = max(ego, R), RW = 2*rad+1 rows of the fused band
-    int rows_words, warp_smem;
-    uint32_t ow_magic, rw_magic, s_magic, n_magic;
+    int bits_words, grp_smem; // obs bit-stream words, shared-memory bytes per lane group
+    uint32_t rw_magic, s_magic, n_magic;
 };
 
 struct SuperParams {
