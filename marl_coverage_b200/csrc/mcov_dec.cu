@@ -26,6 +26,8 @@
 // (4 bits -> one float4 through a 16-entry shared-memory table) and stored with coalesced 128-bit
 // streaming stores straight into the torch buffer.  The next env's header, poses
 // and actions are prefetched into registers while the current env is processed.
+#include <stdlib.h>
+
 #include "mcov_internal.h"
 
 namespace mcov {
@@ -155,6 +157,10 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
     s.winO = s.winF + p.N * p.S;
     s.wallW = s.winO + p.N * p.S;
     return s;
+}
+
+__device__ __forceinline__ void prefetch_l1(const void* ptr) {
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(ptr));
 }
 
 // ORs the low `width` bits of `v` into the bit stream at bit offset `off` (shared-memory atomics:
@@ -301,6 +307,34 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
     g.sync();
 
     const bool do_sense = fresh || (mode == MODE_STEP && !sentinel);
+    if (!fresh) {
+        // Pull the lines under every robot's window towards the SM now: band rows are contiguous in
+        // x within a strip ((2*rad+1) * 8 B <= 2 lines), so touching the first and last row of each
+        // run covers it.  One lane per (robot, strip); the slot loop below then hits L1/L2 instead
+        // of paying one DRAM round trip per iteration.
+        for (int idx = lg; idx < 2 * N; idx += G) {
+            const int i = idx >> 1, k = idx & 1;
+            const uint32_t pi = sm.posF[i];
+            const int xi = unpack_x(pi), yi = unpack_y(pi);
+            const int s = ((yi - rad) >> 5) + k;
+            if (s < 0 || s >= strips || (k == 1 && ((yi - rad) & 31) + RW <= 32)) continue;
+            const int xa = max(xi - rad, 0), xb = min(xi + rad, W - 1);
+            const uint2* fo_i = fo_e + (size_t)i * PW + s * Wp;
+            prefetch_l1(fo_i + xa);
+            prefetch_l1(fo_i + xb);
+            if (do_sense && s >= ((yi - R) >> 5) && s <= ((yi + R) >> 5)) {
+                const int xc = max(xi - R, 0), xd = min(xi + R, W - 1);
+                prefetch_l1(vis + s * Wp + xc);
+                prefetch_l1(vis + s * Wp + xd);
+                prefetch_l1(wall + s * Wp + xc);
+                prefetch_l1(wall + s * Wp + xd);
+                if (!LIDAR) {
+                    prefetch_l1(tpos + s * Wp + xc);
+                    prefetch_l1(tpos + s * Wp + xd);
+                }
+            }
+        }
+    }
     if (do_sense) {
         // which robots' sensor rows can share a bitmap word with robot i's?  (one lane per pair)
         for (int idx = lg; idx < N * N; idx += G) {
@@ -545,13 +579,18 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
 
     // ---- observation block: bit stream -> float32, coalesced 128-bit streaming stores ----------
     float* obs_e = p.obs + (size_t)e * p.obs_env_floats;
+    if (p.debug & 1) return false;                                 // MCOV_DEBUG=1: profiling aid, no obs store
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
         const int nf4 = p.obs_env_floats >> 2;
-        for (int q = lg; q < nf4; q += G) {
-            const uint32_t w = sm.bits[q >> 3] >> ((q & 7) * 4);
-            __stcs(dst + q, lut[w & 15u]);
-        }
+        // float4 q = lg + G*t holds bits [4q, 4q+4): word t*(G/8) + (lg>>3), nibble lg&7
+        const uint32_t* bw = sm.bits + (lg >> 3);
+        const int nib = (lg & 7) * 4;
+        float4* d = dst + lg;
+        const int iters = (nf4 - lg + G - 1) / G;
+#pragma unroll 4
+        for (int t = 0; t < iters; ++t)
+            __stcs(d + t * G, lut[(bw[t * (G / 8)] >> nib) & 15u]);
     } else {
         for (int k = lg; k < p.obs_env_floats; k += G)
             __stcs(obs_e + k, ((sm.bits[k >> 5] >> (k & 31)) & 1u) ? 1.0f : 0.0f);
@@ -776,6 +815,8 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.s_magic = magic_for(p.S);
     p.n_magic = magic_for(p.N);
     const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
+    static const int debug = getenv("MCOV_DEBUG") ? atoi(getenv("MCOV_DEBUG")) : 0;
+    p.debug = debug;
     cudaError_t err;
     if (s.G == 8) err = lidar ? launch_dec_t<8, true>(s, p, st) : launch_dec_t<8, false>(s, p, st);
     else if (s.G == 16) err = lidar ? launch_dec_t<16, true>(s, p, st) : launch_dec_t<16, false>(s, p, st);

@@ -62,6 +62,7 @@ struct DecParams {
     int rad, RW;              // rad = max(ego, R), RW = 2*rad+1 rows of the fused band
     int bits_words, grp_smem; // obs bit-stream words, shared-memory bytes per lane group
     uint32_t rw_magic, s_magic, n_magic;
+    int debug;                // MCOV_DEBUG env bits (profiling aids; 0 in normal use)
 };
 
 struct SuperParams {

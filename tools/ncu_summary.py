@@ -44,31 +44,45 @@ def main():
         st.sort(key=lambda t: -float(t[1].replace(',', '') or 0))
         for name, v in st[:8]:
             print('  stall %-50s %s' % (name.split('issue_stalled_')[1].split('_per_')[0], v))
-    src = page(rep, 'source', ['--print-source', 'cuda'])
-    src = [r for r in src if len(r) > 6]
-    if len(src) > 2:
-        h = src[0]
-        ci, cs, cx = h.index('Source'), h.index('# Samples'), h.index('Instructions Executed')
-        cl = h.index('Address') if 'Address' in h else 0
+    src = page(rep, 'source', ['--print-source', 'cuda,sass'])
+    h = None
+    cur = line = None
+    agg = {}
+    for r in src:
+        if len(r) >= 2 and r[0] == 'File Name':
+            cur = r[1].split('/')[-1]
+            continue
+        if len(r) > 6 and r[0] == 'Line No':
+            h = r
+            continue
+        if h is None or len(r) <= 6:
+            continue
+        if r[0] != '':
+            line = (cur, r[0], r[1].strip())
+            agg.setdefault(line, [0.0, 0.0])
+            continue
+        if r[2] in ('...', ''):
+            continue
+        cs, cx = h.index('# Samples'), h.index('Instructions Executed')
 
         def num(x):
             try:
                 return float(x.replace(',', ''))
             except Exception:
                 return 0.0
-        body = src[1:]
-        tot = sum(num(r[cs]) for r in body) or 1.0
-        toti = sum(num(r[cx]) for r in body) or 1.0
-        print('== source lines by stall samples (total %d samples, %d warp-instr)' % (tot, toti))
-        order = sorted(range(len(body)), key=lambda k: -num(body[k][cs]))
-        for k in order[:nlines]:
-            r = body[k]
-            print('  %5.1f%% smp %5.1f%% inst  L%-4s %s' % (100 * num(r[cs]) / tot, 100 * num(r[cx]) / toti, r[cl], r[ci].strip()[:100]))
-        print('== source lines by instructions executed')
-        order = sorted(range(len(body)), key=lambda k: -num(body[k][cx]))
-        for k in order[:nlines]:
-            r = body[k]
-            print('  %5.1f%% inst %5.1f%% smp  L%-4s %s' % (100 * num(r[cx]) / toti, 100 * num(r[cs]) / tot, r[cl], r[ci].strip()[:100]))
+        agg[line][0] += num(r[cs])
+        agg[line][1] += num(r[cx])
+    if agg:
+        tot = sum(v[0] for v in agg.values()) or 1.0
+        toti = sum(v[1] for v in agg.values()) or 1.0
+        print('== CUDA lines by warp instructions executed (total %d warp-instr, %d stall samples)' % (toti, tot))
+        for k in sorted(agg, key=lambda k: -agg[k][1])[:nlines]:
+            v = agg[k]
+            print('  %5.1f%% inst %5.1f%% smp  %s:%s %s' % (100 * v[1] / toti, 100 * v[0] / tot, k[0], k[1], k[2][:90]))
+        print('== CUDA lines by stall samples')
+        for k in sorted(agg, key=lambda k: -agg[k][0])[:nlines]:
+            v = agg[k]
+            print('  %5.1f%% smp %5.1f%% inst  %s:%s %s' % (100 * v[0] / tot, 100 * v[1] / toti, k[0], k[1], k[2][:90]))
 
 
 if __name__ == '__main__':
