@@ -163,13 +163,13 @@ __device__ __forceinline__ void prefetch_l1(const void* ptr) {
     asm volatile("prefetch.global.L1 [%0];" :: "l"(ptr));
 }
 
-// ORs the low `width` bits of `v` into the bit stream at bit offset `off` (shared-memory atomics:
+// ORs `v` into the bit stream at bit offset `off` (shared-memory atomics:
 // neighbouring rows share words).
-__device__ __forceinline__ void stream_or(uint32_t* bits, int off, uint32_t v, int width) {
-    if (v == 0) return;
+__device__ __forceinline__ void stream_or(uint32_t* bits, int off, uint32_t v) {
     const int w = off >> 5, sh = off & 31;
-    atomicOr(bits + w, v << sh);
-    if (sh + width > 32) atomicOr(bits + w + 1, v >> (32 - sh));
+    const uint32_t lo = v << sh, hi = __funnelshift_l(v, 0u, sh);   // bits of v pushed past bit 31
+    if (lo) atomicOr(bits + w, lo);
+    if (hi) atomicOr(bits + w + 1, hi);
 }
 
 // Sensor-frame helpers.  A robot at (xj, yj) with range R touches, in map row x (|x - xj| <= R),
@@ -182,21 +182,42 @@ __device__ __forceinline__ uint32_t ymask_in_strip(int yj, int R, int S, int s) 
 
 // One pass over env e in `mode`.  Returns true when a finished env must be re-seeded in place by a
 // second (MODE_RESET) pass of the same lane group (fused auto-reset).
-template <int G, bool LIDAR>
+// Compile-time shape of an env (0 = read the value from DecParams at run time).  The named
+// BASELINE configs get their own instantiation so that loop bounds, divisions and masks fold.
+template <int G_, bool LIDAR_, int CN_, int CR_, int CE_>
+struct Spec {
+    static constexpr int G = G_, CN = CN_, CR = CR_, CE = CE_;
+    static constexpr bool LIDAR = LIDAR_;
+    static constexpr bool FIXED = CN_ > 0;             // then C == 3, N, R, ego are constants
+};
+
+template <class SP>
 __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut,
                                          const int e, const int mode, const Prefetch& cur,
-                                         const Grp<G>& g) {
-    const int N = p.N, S = p.S, R = p.R, W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips;
-    const int PW = p.g.PW;
-    const int ow = p.ow, ego = p.ego, C = p.C, rad = p.rad, RW = p.RW;
+                                         const Grp<SP::G>& g) {
+    constexpr int G = SP::G;
+    constexpr bool LIDAR = SP::LIDAR;
+    const int N = SP::FIXED ? SP::CN : p.N, R = SP::FIXED ? SP::CR : p.R, ego = SP::FIXED ? SP::CE : p.ego;
+    const int C = SP::FIXED ? 3 : p.C;
+    const int S = 2 * R + 1, ow = 2 * ego + 1, rad = ego > R ? ego : R, RW = 2 * rad + 1;
+    const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
     const int lg = g.lg;
+    auto div_n = [&](int k) { return SP::FIXED ? k / (SP::FIXED ? SP::CN : 1) : fast_div(k, p.n_magic); };
+    auto div_s = [&](int k) { return SP::FIXED ? k / (2 * SP::CR + 1) : fast_div(k, p.s_magic); };
+    auto div_rw = [&](int k) {
+        return SP::FIXED ? k / (2 * (SP::CE > SP::CR ? SP::CE : SP::CR) + 1) : fast_div(k, p.rw_magic);
+    };
 
     unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
     EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
     uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
     int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
-    uint2* fo_e = p.fo + (size_t)e * N * PW;
-    uint32_t* vis = p.visited + (size_t)e * PW;
+    // 32-bit word offsets from the arena bases (launch_dec checks E*N*PW < 2^32): one IMAD.WIDE per
+    // access instead of carrying / rebuilding 64-bit per-env pointers
+    const uint32_t eN = (uint32_t)e * (uint32_t)N;
+    const uint32_t vis_off = (uint32_t)e * (uint32_t)PW;
+    uint2* const fo_g = p.fo;
+    uint32_t* const vis_g = p.visited;
 
     g.sync();                                    // previous pass has finished reading sm.bits
     const bool fresh = (mode == MODE_RESET);
@@ -208,10 +229,10 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
         map_idx = g.shfl(mi, 0);
         if (!p.skip_wipe) {
             // wipe this env's planes (dec_grid_rl.py:505-514) with 128-bit stores
-            uint4* z = reinterpret_cast<uint4*>(fo_e);
+            uint4* z = reinterpret_cast<uint4*>(fo_g + (size_t)eN * PW);
             const int n16 = N * (PW / 2);
             for (int k = lg; k < n16; k += G) z[k] = make_uint4(0, 0, 0, 0);
-            uint4* zv = reinterpret_cast<uint4*>(vis);
+            uint4* zv = reinterpret_cast<uint4*>(vis_g + vis_off);
             for (int k = lg; k < PW / 4; k += G) zv[k] = make_uint4(0, 0, 0, 0);
         }
         g.sync();
@@ -222,8 +243,9 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
         shown = cur.shown;
         myv = cur.pos;
     }
-    const uint32_t* wall = p.wall + (size_t)map_idx * PW;
-    const uint32_t* tpos = p.pos + (size_t)map_idx * PW;
+    const uint32_t map_off = (uint32_t)map_idx * (uint32_t)PW;
+    const uint32_t* const wall_g = p.wall;
+    const uint32_t* const tpos_g = p.pos;
 
     // early loads for the bookkeeping at the end of the pass (kept in flight until then)
     int cs0 = 0, fc = 1;
@@ -255,7 +277,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
             const int tx = px + (u == 0) - (u == 2);
             const int ty = py + (u == 1) - (u == 3);
             int blocked0 = 1;
-            if (lg < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
+            if (lg < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall_g + map_off, Wp, tx, ty);
             const uint32_t tv = pack_xy(tx, ty);
             uint32_t pv = myv;
             for (int k = 0; k < N; ++k) {
@@ -319,18 +341,18 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
             const int s = ((yi - rad) >> 5) + k;
             if (s < 0 || s >= strips || (k == 1 && ((yi - rad) & 31) + RW <= 32)) continue;
             const int xa = max(xi - rad, 0), xb = min(xi + rad, W - 1);
-            const uint2* fo_i = fo_e + (size_t)i * PW + s * Wp;
-            prefetch_l1(fo_i + xa);
-            prefetch_l1(fo_i + xb);
+            const uint32_t fw = (eN + i) * PW + s * Wp;
+            prefetch_l1(fo_g + fw + xa);
+            prefetch_l1(fo_g + fw + xb);
             if (do_sense && s >= ((yi - R) >> 5) && s <= ((yi + R) >> 5)) {
                 const int xc = max(xi - R, 0), xd = min(xi + R, W - 1);
-                prefetch_l1(vis + s * Wp + xc);
-                prefetch_l1(vis + s * Wp + xd);
-                prefetch_l1(wall + s * Wp + xc);
-                prefetch_l1(wall + s * Wp + xd);
+                prefetch_l1(vis_g + vis_off + s * Wp + xc);
+                prefetch_l1(vis_g + vis_off + s * Wp + xd);
+                prefetch_l1(wall_g + map_off + s * Wp + xc);
+                prefetch_l1(wall_g + map_off + s * Wp + xd);
                 if (!LIDAR) {
-                    prefetch_l1(tpos + s * Wp + xc);
-                    prefetch_l1(tpos + s * Wp + xd);
+                    prefetch_l1(tpos_g + map_off + s * Wp + xc);
+                    prefetch_l1(tpos_g + map_off + s * Wp + xd);
                 }
             }
         }
@@ -338,7 +360,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
     if (do_sense) {
         // which robots' sensor rows can share a bitmap word with robot i's?  (one lane per pair)
         for (int idx = lg; idx < N * N; idx += G) {
-            const int i = fast_div(idx, p.n_magic), j = idx - i * N;
+            const int i = div_n(idx), j = idx - i * N;
             const uint32_t pi = sm.posF[i], pj = sm.posF[j];
             const int yi = unpack_y(pi), yj = unpack_y(pj);
             const bool nr = (i != j) && abs(unpack_x(pi) - unpack_x(pj)) <= 2 * R &&
@@ -348,10 +370,10 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
         if (LIDAR) {
             // lidar.py:16-65 — stage the truth wall window, then march beams in float64
             for (int idx = lg; idx < N * S; idx += G) {
-                const int i = fast_div(idx, p.s_magic), r = idx - i * S;
+                const int i = div_s(idx), r = idx - i * S;
                 const uint32_t pi = sm.posF[i];
                 const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
-                sm.wallW[idx] = (x >= 0 && x < W) ? read_window(wall, Wp, strips, x, y0, S) : 0xffffffffu;
+                sm.wallW[idx] = (x >= 0 && x < W) ? read_window(wall_g + map_off, Wp, strips, x, y0, S) : 0xffffffffu;
                 sm.winF[idx] = 0;
                 sm.winO[idx] = 0;
             }
@@ -386,7 +408,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
             if (p.single_tool) {
                 g.sync();
                 for (int idx = lg; idx < N * S; idx += G) {
-                    const int i = fast_div(idx, p.s_magic), r = idx - i * S;
+                    const int i = div_s(idx), r = idx - i * S;
                     sm.winF[idx] = (r == R) ? (1u << R) : 0u;      // dec_grid_rl.py:233-234
                 }
             }
@@ -404,110 +426,109 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
     const uint32_t wm_ow = low_mask(ow);
     const int ow2 = ow * ow;
     for (int idx = lg; idx < total; idx += G) {
-        const int i = fast_div(idx, p.rw_magic), a2 = idx - i * RW;
+        const int i = div_rw(idx), a2 = idx - i * RW;
         const uint32_t pi = sm.posF[i];
         const int xi = unpack_x(pi), yi = unpack_y(pi);
         const int x = xi - rad + a2;
-        const bool inx = x >= 0 && x < W;
+        const bool inx = (unsigned)x < (unsigned)W;
         const int y0r = yi - rad, s0 = y0r >> 5, sh = y0r & 31;
-        const bool in0 = inx && s0 >= 0 && s0 < strips;
-        const bool in1 = inx && (sh + RW > 32) && s0 + 1 >= 0 && s0 + 1 < strips;
-        const int w0 = s0 * Wp + x;
-        uint2* fo_i = fo_e + (size_t)i * PW;
-        const bool sens = do_sense && inx && abs(x - xi) <= R;
+        const bool in0 = inx && (unsigned)s0 < (unsigned)strips;
+        const bool in1 = inx && (sh + RW > 32) && (unsigned)(s0 + 1) < (unsigned)strips;
+        const uint32_t w0 = (uint32_t)(s0 * Wp + x);             // only dereferenced under in0 / in1
+        const uint32_t fw = (eN + (uint32_t)i) * (uint32_t)PW + w0;
+        const bool sens = do_sense && inx && abs(a2 - rad) <= R;
+        const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
+        const bool q0 = sens && in0, q1 = sens && in1;
+        const bool t0 = q0 && s0 == ys0, t1 = q1 && s0 + 1 <= ys1;   // words the sensor rows touch
 
         uint2 lo = make_uint2(0, 0), hi = make_uint2(0, 0);
+        uint32_t vlo = 0, vhi = 0;
         if (!fresh) {
-            if (in0) lo = fo_i[w0];
-            if (in1) hi = fo_i[w0 + Wp];
+            if (in0) lo = fo_g[fw];
+            if (in1) hi = fo_g[fw + Wp];
+            if (t0) vlo = vis_g[vis_off + w0];
+            if (t1) vhi = vis_g[vis_off + w0 + Wp];
         }
-        uint2 nlo = lo, nhi = hi;
-        if (sens) {
-            const int ys0 = (yi - R) >> 5, ys1 = (yi + R) >> 5;
-            const bool t0 = in0 && s0 >= ys0, t1 = in1 && s0 + 1 <= ys1;
-            uint32_t vlo = 0, vhi = 0;
-            if (!fresh) {
-                if (t0) vlo = vis[w0];
-                if (t1) vhi = vis[w0 + Wp];
+        uint32_t f0 = 0, f1 = 0, o0 = 0, o1 = 0;
+        if (!LIDAR) {
+            // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
+            const uint64_t m64 = (uint64_t)low_mask(S) << (sh + rad - R);
+            const uint32_t m0 = (uint32_t)m64, m1 = (uint32_t)(m64 >> 32);
+            if (q0) { o0 = __ldg(&wall_g[map_off + w0]) & m0; f0 = __ldg(&tpos_g[map_off + w0]) & m0; }
+            if (q1) { o1 = __ldg(&wall_g[map_off + w0 + Wp]) & m1; f1 = __ldg(&tpos_g[map_off + w0 + Wp]) & m1; }
+            if (p.single_tool) {                                   // dec_grid_rl.py:233-234
+                const uint64_t c64 = (a2 == rad) ? (1ull << (sh + rad)) : 0ull;
+                f0 = q0 ? (uint32_t)c64 : 0u;
+                f1 = q1 ? (uint32_t)(c64 >> 32) : 0u;
             }
-            uint32_t f0 = 0, f1 = 0, o0 = 0, o1 = 0;
-            if (!LIDAR) {
-                // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
-                const uint64_t m64 = (uint64_t)low_mask(S) << (sh + rad - R);
-                const uint32_t m0 = (uint32_t)m64, m1 = (uint32_t)(m64 >> 32);
-                if (in0) { o0 = __ldg(wall + w0) & m0; f0 = __ldg(tpos + w0) & m0; }
-                if (in1) { o1 = __ldg(wall + w0 + Wp) & m1; f1 = __ldg(tpos + w0 + Wp) & m1; }
-                if (p.single_tool) {                               // dec_grid_rl.py:233-234
-                    const uint64_t c64 = (x == xi) ? (1ull << (sh + rad)) : 0ull;
-                    f0 = in0 ? (uint32_t)c64 : 0u;
-                    f1 = in1 ? (uint32_t)(c64 >> 32) : 0u;
-                }
-            } else {
-                const int r = x - xi + R;
-                split_words(sm.winF[i * S + r] << (rad - R), y0r, f0, f1);
-                split_words(sm.winO[i * S + r] << (rad - R), y0r, o0, o1);
-                if (!in0) { f0 = 0; o0 = 0; }
-                if (!in1) { f1 = 0; o1 = 0; }
-            }
-            // per-robot memory: free_i |= hits, obst_i |= hits  (dec_grid_rl.py:231-236)
-            nlo = make_uint2(lo.x | f0, lo.y | o0);
-            nhi = make_uint2(hi.x | f1, hi.y | o1);
-            const int cn = __popc(f0 & ~lo.x) + __popc(f1 & ~hi.x);
-            if (in0 && (nlo.x != lo.x || nlo.y != lo.y)) fo_i[w0] = nlo;
-            if (in1 && (nhi.x != hi.x || nhi.y != hi.y)) fo_i[w0 + Wp] = nhi;
-            if (cn) atomicAdd(&sm.covS[i], cn);                     // shared-memory atomic
-            // union "visited" plane: exactly one writer per word (dec_grid_rl.py:243-256)
-            const uint32_t nm = sm.nearM[i];
+        } else if (sens) {
+            const int r = a2 - rad + R;
+            split_words(sm.winF[i * S + r] << (rad - R), y0r, f0, f1);
+            split_words(sm.winO[i * S + r] << (rad - R), y0r, o0, o1);
+            if (!in0) { f0 = 0; o0 = 0; }
+            if (!in1) { f1 = 0; o1 = 0; }
+        }
+        // per-robot memory: free_i |= hits, obst_i |= hits  (dec_grid_rl.py:231-236)
+        const uint2 nlo = make_uint2(lo.x | f0, lo.y | o0);
+        const uint2 nhi = make_uint2(hi.x | f1, hi.y | o1);
+        const int cn = __popc(f0 & ~lo.x) + __popc(f1 & ~hi.x);
+        if ((f0 & ~lo.x) | (o0 & ~lo.y)) fo_g[fw] = nlo;
+        if ((f1 & ~hi.x) | (o1 & ~hi.y)) fo_g[fw + Wp] = nhi;
+        if (cn) atomicAdd(&sm.covS[i], cn);                         // shared-memory atomic
+        // union "visited" plane: exactly one writer per word (dec_grid_rl.py:243-256)
+        uint32_t comb0 = f0, comb1 = f1;
+        bool own0 = t0, own1 = t1;
+        const uint32_t nm = sens ? sm.nearM[i] : 0u;
+        if (nm) {                                                   // rare: footprints overlap
+            for (uint32_t mm = nm; mm; mm &= mm - 1) {
+                const int j = __ffs(mm) - 1;
+                const uint32_t pj = sm.posF[j];
+                const int xj = unpack_x(pj), yj = unpack_y(pj);
+                if (abs(x - xj) > R) continue;
+                const int y0j = yj - R, s0j = y0j >> 5, s1j = (yj + R) >> 5;
 #pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                if (!(k == 0 ? t0 : t1)) continue;
-                const int s = s0 + k;
-                uint32_t comb = k == 0 ? f0 : f1;
-                bool owner = true;
-                for (uint32_t mm = nm; mm; mm &= mm - 1) {          // rare: footprints overlap
-                    const int j = __ffs(mm) - 1;
-                    const uint32_t pj = sm.posF[j];
-                    const int xj = unpack_x(pj), yj = unpack_y(pj);
-                    if (abs(x - xj) > R) continue;
-                    const int y0j = yj - R, s0j = y0j >> 5;
-                    if (s < s0j || s > ((yj + R) >> 5)) continue;
-                    owner &= (j > i);
+                for (int k = 0; k < 2; ++k) {
+                    const int sk = s0 + k;
+                    if (!(k == 0 ? t0 : t1) || sk < s0j || sk > s1j) continue;
+                    uint32_t add;
                     if (LIDAR) {
                         uint32_t jl, jh;
                         split_words(sm.winF[j * S + (x - xj + R)], y0j, jl, jh);
-                        comb |= (s == s0j) ? jl : jh;
+                        add = (sk == s0j) ? jl : jh;
                     } else if (p.single_tool) {
-                        comb |= (x == xj && (yj >> 5) == s) ? (1u << (yj & 31)) : 0u;
+                        add = (x == xj && (yj >> 5) == sk) ? (1u << (yj & 31)) : 0u;
                     } else {
-                        comb |= __ldg(tpos + w0 + k * Wp) & ymask_in_strip(yj, R, S, s);
+                        add = __ldg(&tpos_g[map_off + w0 + k * Wp]) & ymask_in_strip(yj, R, S, sk);
                     }
-                }
-                if (owner) {
-                    const uint32_t vold = k == 0 ? vlo : vhi;
-                    const uint32_t nb = comb & ~vold;
-                    cnt += __popc(nb);
-                    if (nb) vis[w0 + k * Wp] = vold | comb;
+                    if (k == 0) { comb0 |= add; own0 = own0 && (j > i); }
+                    else { comb1 |= add; own1 = own1 && (j > i); }
                 }
             }
         }
+        {
+            const uint32_t nb0 = own0 ? (comb0 & ~vlo) : 0u, nb1 = own1 ? (comb1 & ~vhi) : 0u;
+            cnt += __popc(nb0) + __popc(nb1);
+            if (nb0) vis_g[vis_off + w0] = vlo | comb0;
+            if (nb1) vis_g[vis_off + w0 + Wp] = vhi | comb1;
+        }
         // egocentric observation rows (dec_grid_rl.py:334-347): layers 1 (free_i) and 2 (obst_i)
         const int a = a2 - (rad - ego);
-        if (a >= 0 && a < ow) {
+        if ((unsigned)a < (unsigned)ow) {
             const uint32_t bF = (__funnelshift_r(nlo.x, nhi.x, sh) >> (rad - ego)) & wm_ow;
             const uint32_t bO = (__funnelshift_r(nlo.y, nhi.y, sh) >> (rad - ego)) & wm_ow;
             const int off = ((i * C + 1) * ow + a) * ow;
-            stream_or(sm.bits, off, bF, ow);
-            stream_or(sm.bits, off + ow2, bO, ow);
+            stream_or(sm.bits, off, bF);
+            stream_or(sm.bits, off + ow2, bO);
         }
     }
     // layer 0 shows every robot that has moved at least once (quirk A.3.4): one lane per
     // (viewer i, shown robot j) pair
     for (int idx = lg; idx < N * N; idx += G) {
-        const int i = fast_div(idx, p.n_magic), j = idx - i * N;
+        const int i = div_n(idx), j = idx - i * N;
         if (!((shown >> j) & 1u)) continue;
         const uint32_t pi = sm.posF[i], pj = sm.posF[j];
         const int a = unpack_x(pj) - (unpack_x(pi) - ego), b = unpack_y(pj) - (unpack_y(pi) - ego);
-        if (a >= 0 && a < ow && b >= 0 && b < ow) stream_or(sm.bits, (i * C * ow + a) * ow + b, 1u, 1);
+        if (a >= 0 && a < ow && b >= 0 && b < ow) stream_or(sm.bits, (i * C * ow + a) * ow + b, 1u);
     }
     g.sync();
 
@@ -598,9 +619,10 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
     return false;
 }
 
-template <int G, bool LIDAR>
+template <class SP>
 __global__ void __launch_bounds__(MAX_WARPS * 32, 4)
 dec_env_kernel(const DecParams p) {
+    constexpr int G = SP::G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ float4 lut[16];
     __shared__ int last_flag;
@@ -632,7 +654,7 @@ dec_env_kernel(const DecParams p) {
             else if (p.mask_from_flags) act = p.needs_reset[e];
             if (!act) continue;                                    // group-uniform
         }
-        while (env_pass<G, LIDAR>(p, sm, lut, e, m, cur, g)) m = MODE_RESET;   // fused auto-reset
+        while (env_pass<SP>(p, sm, lut, e, m, cur, g)) m = MODE_RESET;   // fused auto-reset
     }
 
     // ---- episode statistics: group sums -> CTA row -> last CTA folds all rows (single launch) --
@@ -790,14 +812,14 @@ inline DecLaunchShape dec_shape(const mcov_env* env) {
 
 inline uint32_t magic_for(int d) { return (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); }
 
-template <int G, bool LIDAR>
+template <class SP>
 cudaError_t launch_dec_t(const DecLaunchShape& s, const DecParams& p, cudaStream_t st) {
     if (s.smem > 48 * 1024) {
-        cudaError_t err = cudaFuncSetAttribute(dec_env_kernel<G, LIDAR>,
+        cudaError_t err = cudaFuncSetAttribute(dec_env_kernel<SP>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
         if (err != cudaSuccess) return err;
     }
-    dec_env_kernel<G, LIDAR><<<s.grid, s.threads, s.smem, st>>>(p);
+    dec_env_kernel<SP><<<s.grid, s.threads, s.smem, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -817,10 +839,16 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
     static const int debug = getenv("MCOV_DEBUG") ? atoi(getenv("MCOV_DEBUG")) : 0;
     p.debug = debug;
+    if ((uint64_t)p.E * p.N * p.g.PW >= 0xffffffffull) return cudaErrorInvalidValue;   // 32-bit word offsets
     cudaError_t err;
-    if (s.G == 8) err = lidar ? launch_dec_t<8, true>(s, p, st) : launch_dec_t<8, false>(s, p, st);
-    else if (s.G == 16) err = lidar ? launch_dec_t<16, true>(s, p, st) : launch_dec_t<16, false>(s, p, st);
-    else err = lidar ? launch_dec_t<32, true>(s, p, st) : launch_dec_t<32, false>(s, p, st);
+    const bool plain = p.C == 3;
+    // instantiations for the BASELINE configs (C2/C5, C3, C4), generic otherwise
+    if (plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(s, p, st);
+    else if (plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5) err = launch_dec_t<Spec<8, true, 8, 10, 5>>(s, p, st);
+    else if (plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5) err = launch_dec_t<Spec<16, false, 16, 2, 5>>(s, p, st);
+    else if (s.G == 8) err = lidar ? launch_dec_t<Spec<8, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<8, false, 0, 0, 0>>(s, p, st);
+    else if (s.G == 16) err = lidar ? launch_dec_t<Spec<16, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<16, false, 0, 0, 0>>(s, p, st);
+    else err = lidar ? launch_dec_t<Spec<32, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<32, false, 0, 0, 0>>(s, p, st);
     env->launches++;
     return err;
 }
