@@ -91,6 +91,9 @@ unsigned char* scratch_dist_term(const mcov_env* env) { return scratch_counter(e
 unsigned char* scratch_moves(const mcov_env* env) {
     return scratch_dist_term(env) + align_up64((int64_t)env->cfg.num_envs * 4, 256);
 }
+unsigned char* scratch_super_dt(const mcov_env* env) {
+    return scratch_moves(env) + align_up64((int64_t)env->cfg.num_envs * 8, 256);
+}
 
 int check_ready(const mcov_env* env) {
     if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
@@ -318,6 +321,7 @@ int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_d
     off = align_up64(off + 256, 256);
     off = align_up64(off + E * 4, 256);
     off = align_up64(off + E * 8, 256);
+    if (c.env_type == MCOV_ENV_SUPER) off = align_up64(off + mcov::super_dt_scratch_bytes(env), 256);
     l.total_bytes = off;
     return MCOV_OK;
 }
@@ -441,14 +445,14 @@ static int run_super(mcov_env* env, int mode, const void* actions, int act_fmt, 
     p.reward = reward;
     p.reward64 = reward64;
     p.done = done;
-    double* partial = reinterpret_cast<double*>(env->arena + env->lay.off_scratch);
-    p.stats_partial = (stats && mode == mcov::MODE_STEP) ? partial : nullptr;
+    p.stats_partial = reinterpret_cast<double*>(env->arena + env->lay.off_scratch);
+    p.stats_out = (mode == mcov::MODE_STEP) ? stats : nullptr;
+    p.counter = reinterpret_cast<unsigned int*>(scratch_counter(env));
+    p.dt_scratch = mcov::super_dt_scratch_bytes(env) > 0
+                       ? reinterpret_cast<uint16_t*>(scratch_super_dt(env)) : nullptr;
+    p.vec_ok = (env->g.L % 4 == 0) && aligned(obs, 16);
     cudaError_t ce = mcov::launch_super(env, p, st);
     if (ce != cudaSuccess) return cuda_fail(ce, "super kernel launch");
-    if (p.stats_partial) {
-        ce = mcov::launch_stats_reduce(env, partial, mcov::super_grid_size(env), stats, st);
-        if (ce != cudaSuccess) return cuda_fail(ce, "stats reduce launch");
-    }
     return MCOV_OK;
 }
 
@@ -492,13 +496,9 @@ int mcov_step(mcov_env* env, const void* actions_dev, int action_format, float* 
     if (dec)   // DecGridRL: the re-seed is fused into the step kernel (one launch per step)
         return run_dec(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, seed,
                        obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
-    rc = run_super(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, 0,
-                   obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
-    if (rc) return rc;
-    if (env->cfg.auto_reset)
-        rc = run_super(env, mcov::MODE_RESET, nullptr, 0, nullptr, 1, nullptr, nullptr, seed,
-                       obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
-    return rc;
+    // SuperGridRL: same single-launch scheme
+    return run_super(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, seed,
+                     obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);
 }
 
 int mcov_observe(mcov_env* env, float* obs_out_dev, void* stream) {

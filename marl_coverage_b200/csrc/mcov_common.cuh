@@ -99,6 +99,59 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 // unbiased-enough bounded draw: floor(u * n / 2^32)
 __device__ __forceinline__ int bounded(uint32_t u, int n) { return (int)__umulhi(u, (uint32_t)n); }
 
+// ---- packed poses ------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_xy(int x, int y) {
+    return (uint32_t)(x & 0xffff) | ((uint32_t)(y & 0xffff) << 16);
+}
+__device__ __forceinline__ int unpack_x(uint32_t v) { return (int)(int16_t)(v & 0xffffu); }
+__device__ __forceinline__ int unpack_y(uint32_t v) { return (int)(int16_t)(v >> 16); }
+
+// Episode start draw (dec_grid_rl.py:462-502, super_grid_rl.py:354-388): uniform map, then N
+// distinct walkable cells by rejection over the whole (bordered) map.  Same distribution as the
+// reference, not numpy's Mersenne-Twister stream: Philox keyed by `seed`, counter = (global env
+// id, episode, draw).  `map_idx_in` / `start_xy_in` (nullable) inject the draw instead.
+__device__ inline void draw_starts(const uint32_t* __restrict__ wall_table, const Geometry& g, int N,
+                                   int n_maps, const int32_t* map_idx_in, const int16_t* start_xy_in,
+                                   uint64_t seed, uint32_t gid, int e, uint32_t episode,
+                                   uint32_t* posS, int* map_out) {
+    const uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+    int mi;
+    if (map_idx_in) {
+        mi = map_idx_in[e];
+    } else {
+        const uint4 r = philox4x32_10(make_uint4(gid, episode, 0u, 0x4D434F56u), key);
+        mi = bounded(r.x, n_maps);
+    }
+    *map_out = mi;
+    if (start_xy_in) {
+        const int16_t* s = start_xy_in + (size_t)e * N * 2;
+        for (int j = 0; j < N; ++j) posS[j] = pack_xy(s[2 * j], s[2 * j + 1]);
+        return;
+    }
+    const uint32_t* wall = wall_table + (size_t)mi * g.PW;
+    int placed = 0;
+    for (uint32_t k = 1; placed < N && k < 8192u; ++k) {
+        const uint4 r = philox4x32_10(make_uint4(gid, episode, k, 0x4D434F56u), key);
+        const uint32_t cand[4] = {r.x, r.y, r.z, r.w};
+        for (int h = 0; h < 2 && placed < N; ++h) {
+            const int x = bounded(cand[2 * h], g.W), y = bounded(cand[2 * h + 1], g.L);
+            if (get_bit(wall, g.Wp, x, y)) continue;
+            bool taken = false;
+            for (int j = 0; j < placed; ++j) taken |= (posS[j] == pack_xy(x, y));
+            if (!taken) posS[placed++] = pack_xy(x, y);
+        }
+    }
+    // pathological map (almost no walkable cell): deterministic scan so the kernel always ends
+    for (int x = 0; x < g.W && placed < N; ++x)
+        for (int y = 0; y < g.L && placed < N; ++y) {
+            if (get_bit(wall, g.Wp, x, y)) continue;
+            bool taken = false;
+            for (int j = 0; j < placed; ++j) taken |= (posS[j] == pack_xy(x, y));
+            if (!taken) posS[placed++] = pack_xy(x, y);
+        }
+    for (; placed < N; ++placed) posS[placed] = pack_xy(0, 0);
+}
+
 // ---- async bulk (TMA engine) store of a contiguous shared-memory block --------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);

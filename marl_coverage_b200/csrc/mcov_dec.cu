@@ -37,55 +37,13 @@ namespace {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MAX_WARPS = 8;
 
-__device__ __forceinline__ uint32_t pack_xy(int x, int y) {
-    return (uint32_t)(x & 0xffff) | ((uint32_t)(y & 0xffff) << 16);
-}
-__device__ __forceinline__ int unpack_x(uint32_t v) { return (int)(int16_t)(v & 0xffffu); }
-__device__ __forceinline__ int unpack_y(uint32_t v) { return (int)(int16_t)(v >> 16); }
-
 // floor(k / d) for k < 2^26, d <= 64, magic = ceil(2^32 / d)
 __device__ __forceinline__ int fast_div(int k, uint32_t magic) { return (int)__umulhi((uint32_t)k, magic); }
 
-// Draws map + start poses on the device: uniform map, uniform distinct walkable cells by rejection
-// (same distribution as dec_grid_rl.py:462-502; not numpy's Mersenne-Twister stream).
+// Draws map + start poses on the device (see draw_starts in mcov_common.cuh).
 __device__ void draw_reset(const DecParams& p, int e, uint32_t episode, uint32_t* posS, int* map_out) {
-    const uint2 key = make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
-    const uint32_t gid = (uint32_t)(p.env_id_base + e);
-    int mi;
-    if (p.map_idx_in) {
-        mi = p.map_idx_in[e];
-    } else {
-        const uint4 r = philox4x32_10(make_uint4(gid, episode, 0u, 0x4D434F56u), key);
-        mi = bounded(r.x, p.n_maps);
-    }
-    *map_out = mi;
-    if (p.start_xy_in) {
-        const int16_t* s = p.start_xy_in + (size_t)e * p.N * 2;
-        for (int j = 0; j < p.N; ++j) posS[j] = pack_xy(s[2 * j], s[2 * j + 1]);
-        return;
-    }
-    const uint32_t* wall = p.wall + (size_t)mi * p.g.PW;
-    int placed = 0;
-    for (uint32_t k = 1; placed < p.N && k < 8192u; ++k) {
-        const uint4 r = philox4x32_10(make_uint4(gid, episode, k, 0x4D434F56u), key);
-        const uint32_t cand[4] = {r.x, r.y, r.z, r.w};
-        for (int h = 0; h < 2 && placed < p.N; ++h) {
-            const int x = bounded(cand[2 * h], p.g.W), y = bounded(cand[2 * h + 1], p.g.L);
-            if (get_bit(wall, p.g.Wp, x, y)) continue;
-            bool taken = false;
-            for (int j = 0; j < placed; ++j) taken |= (posS[j] == pack_xy(x, y));
-            if (!taken) posS[placed++] = pack_xy(x, y);
-        }
-    }
-    // pathological map (almost no walkable cell): deterministic scan so the kernel always ends
-    for (int x = 0; x < p.g.W && placed < p.N; ++x)
-        for (int y = 0; y < p.g.L && placed < p.N; ++y) {
-            if (get_bit(wall, p.g.Wp, x, y)) continue;
-            bool taken = false;
-            for (int j = 0; j < placed; ++j) taken |= (posS[j] == pack_xy(x, y));
-            if (!taken) posS[placed++] = pack_xy(x, y);
-        }
-    for (; placed < p.N; ++placed) posS[placed] = pack_xy(0, 0);
+    draw_starts(p.wall, p.g, p.N, p.n_maps, p.map_idx_in, p.start_xy_in, p.seed,
+                (uint32_t)(p.env_id_base + e), e, episode, posS, map_out);
 }
 
 // ---- lane groups: G consecutive lanes (8, 16 or 32) own one env; a warp steps 32/G envs at once.

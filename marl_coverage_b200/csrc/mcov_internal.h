@@ -94,7 +94,14 @@ struct SuperParams {
     float* reward;
     double* reward64;
     uint8_t* done;
-    double* stats_partial;
+    double* stats_partial;    // [gridDim][MCOV_STATS_LEN] scratch rows
+    double* stats_out;        // [MCOV_STATS_LEN] or null: folded by the last CTA of the launch
+    unsigned int* counter;    // CTA arrival counter for that fold (zero between launches)
+    // distance-transform work buffer: uint16 [W][dt_pitch] per CTA, in shared memory when it fits,
+    // otherwise one slice per CTA of a global scratch area inside the arena
+    uint16_t* dt_scratch;     // null -> shared memory
+    int dt_pitch;             // uint16 elements per x row (2 * odd number of words)
+    int vec_ok;               // L % 4 == 0 and obs 16-byte aligned: float4 stores
 };
 
 }  // namespace mcov
@@ -128,4 +135,5 @@ cudaError_t launch_init_headers(mcov_env* env, cudaStream_t st);
 cudaError_t launch_percent_covered(mcov_env* env, double* out, cudaStream_t st);
 int dec_grid_size(const mcov_env* env);
 int super_grid_size(const mcov_env* env);
+int64_t super_dt_scratch_bytes(const mcov_env* env);   // 0 when the buffer lives in shared memory
 }  // namespace mcov

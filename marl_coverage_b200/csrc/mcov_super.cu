@@ -1,7 +1,551 @@
-// mcov_super.cu — SuperGridRL kernels (placeholder until the Dec path is parity-green on a B200).
+// mcov_super.cu — SuperGridRL reset/step/get_state as ONE fused sm_100a kernel per call.
+//
+// Reference semantics restated here (file:line in ExistentialRobotics/MARL-Coverage):
+//   SuperGridRL.step          Environments/super_grid_rl.py:74-225
+//   motion_penalty            Environments/super_grid_rl.py:227-243   (first-step quirk)
+//   isInBounds / isOccupied   Environments/super_grid_rl.py:245-279
+//   get_distance_map          Environments/super_grid_rl.py:281-303   (cv2 DIST_L1, restated exactly)
+//   get_state / get_pos_image Environments/super_grid_rl.py:305-341
+//   reset                     Environments/super_grid_rl.py:343-399
+//   done / percent_covered    Environments/super_grid_rl.py:401-421
+//
+// Mapping: one CTA owns one env per loop iteration (persistent CTA-stride loop).  Warp 0 resolves
+// the N sequential collision-checked moves (poses live in lanes, shuffle + ballot), then stamps the
+// (2r+1)^2 footprints robot by robot (lanes = footprint rows) into the bit-packed `covered` /
+// `seen_obst` planes and counts the newly covered cells with __popc; the float64 reward is
+// accumulated in the reference's raster order so it is bit-identical even with a fractional
+// free_penalty.  The whole CTA then rebuilds the L1 distance channel (closed-form bit pass along y,
+// min-plus sweep along x on a uint16 work buffer in shared memory) and streams the (N+3) x W x L
+// float32 state — 280 kB per env at 4 agents / 100x100, the HBM-write-bound part — with 128-bit
+// streaming stores straight into the torch buffer.  Finished envs are re-seeded by the same CTA in
+// the same launch (fused auto-reset); episode statistics are folded by the last CTA.
 #include "mcov_internal.h"
 
 namespace mcov {
-int super_grid_size(const mcov_env* env) { return env->num_sms; }
-cudaError_t launch_super(mcov_env*, SuperParams&, cudaStream_t) { return cudaErrorNotSupported; }
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+constexpr int ST = 512;                       // threads per CTA
+constexpr int DINF = 0xffff;                  // "no zero pixel in reach" (> W + L for any int16 map)
+constexpr int MAXS = 2 * MCOV_MAX_RADIUS + 1;
+
+struct SuperSmem {
+    double stats[MCOV_STATS_LEN];             // running sums of this CTA (thread 0 only)
+    double rew[MCOV_MAX_ROBOTS];              // per control-slot rewards (super_grid_rl.py:104)
+    float4 lut[16];                           // 4 bits -> float4
+    uint2 rows[MCOV_MAX_ROBOTS * MAXS];       // per (robot, footprint row): .x new cells worth 1, .y re-covered
+    uint32_t pos[MCOV_MAX_ROBOTS];            // poses after the moves
+    int any_zero, dmax, covered, again, skip, last;
+};
+
+// ---- exact L1 distance transform -----------------------------------------------------------------
+// d[x][y] = taxicab distance from (x, y) to the nearest NOT-covered in-map cell (0 on such cells),
+// what cv2.distanceTransform(DIST_L1, DIST_MASK_PRECISE) returns at super_grid_rl.py:295.
+// Pass 1 runs along y in closed form on the bit words; pass 2 is the min-plus sweep along x.
+// Layout: uint16 d[x * pitch + y], pitch = 2 * (odd word count) so that both passes and the state
+// writer touch consecutive shared-memory banks.
+__device__ void l1_transform(const uint32_t* cov, const Geometry& g, uint16_t* d, int pitch,
+                             SuperSmem& sm) {
+    const int W = g.W, L = g.L, Wp = g.Wp, strips = g.strips;
+    const int lastbits = L & 31;
+    if (threadIdx.x == 0) { sm.any_zero = 0; sm.dmax = 0; }
+    __syncthreads();
+    int anyz = 0;
+    const int nw = W * strips;
+    for (int idx = threadIdx.x; idx < nw; idx += blockDim.x) {
+        const int s = idx / W, x = idx - s * W;              // x fastest within a strip
+        auto zero_word = [&](int ss) -> uint32_t {
+            const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
+            return ~cov[ss * Wp + x] & valid;
+        };
+        const uint32_t z = zero_word(s);
+        anyz |= (z != 0u);
+        int base_lo = DINF, base_hi = DINF;                  // gap to the nearest zero pixel in other strips
+        for (int ss = s - 1; ss >= 0; --ss) {
+            const uint32_t t = zero_word(ss);
+            if (t) { base_lo = 32 * (s - ss) - (31 - __clz(t)); break; }
+        }
+        for (int ss = s + 1; ss < strips; ++ss) {
+            const uint32_t t = zero_word(ss);
+            if (t) { base_hi = 32 * (ss - s) + (__ffs(t) - 1) - 31; break; }
+        }
+        uint32_t* drow = reinterpret_cast<uint32_t*>(d + (size_t)x * pitch + 32 * s);
+#pragma unroll 4
+        for (int j = 0; j < 16; ++j) {
+            uint32_t packed = 0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int b = 2 * j + h;
+                const uint32_t mlo = z & (FULL >> (31 - b)), mhi = z & (FULL << b);
+                const int dl = mlo ? b - (31 - __clz(mlo)) : b + base_lo;
+                const int dh = mhi ? (__ffs(mhi) - 1) - b : (31 - b) + base_hi;
+                const int v = min(min(dl, dh), DINF);
+                packed |= (uint32_t)v << (16 * h);
+            }
+            drow[j] = packed;
+        }
+    }
+    anyz = __syncthreads_or(anyz);
+    int mx = 0;
+    for (int y = threadIdx.x; y < L; y += blockDim.x) {
+        uint16_t* col = d + y;
+        int v = DINF;
+        for (int x0 = 0; x0 < W; x0 += 8) {
+            int t[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = (x0 + k < W) ? (int)col[(size_t)(x0 + k) * pitch] : DINF;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                v = min(t[k], v + 1);
+                v = min(v, DINF);
+                if (x0 + k < W) col[(size_t)(x0 + k) * pitch] = (uint16_t)v;
+            }
+        }
+        v = DINF;
+        for (int x0 = W - 1; x0 >= 0; x0 -= 8) {
+            int t[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = (x0 - k >= 0) ? (int)col[(size_t)(x0 - k) * pitch] : DINF;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                if (x0 - k >= 0) {
+                    v = min(t[k], v + 1);
+                    v = min(v, DINF);
+                    col[(size_t)(x0 - k) * pitch] = (uint16_t)v;
+                    mx = max(mx, v);
+                }
+            }
+        }
+    }
+    mx = __reduce_max_sync(FULL, mx);
+    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(&sm.dmax, mx);
+    if (threadIdx.x == 0) sm.any_zero = anyz;
+    __syncthreads();
+}
+
+// float32 value of the distance channel: 1 - d / max(d)  (super_grid_rl.py:297-303, all float32)
+__device__ __forceinline__ float dist_value(int dv, int any_zero, int dmax) {
+    if (!any_zero) return 0.0f;                               // cv2: FLT_MAX everywhere -> 1 - 1
+    if (dmax <= 0) return 1.0f;                               // nothing covered yet: no division
+    return __fsub_rn(1.0f, __fdiv_rn((float)dv, (float)dmax));
+}
+
+// np.sum of a float64 vector the way numpy adds it (pairwise_sum with 8 accumulators for n >= 8;
+// verified against numpy 2.3 for every n <= 32) — super_grid_rl.py:214.
+__device__ double numpy_sum(const double* a, int n) {
+    if (n < 8) {
+        double r = 0.0;
+        for (int i = 0; i < n; ++i) r = __dadd_rn(r, a[i]);
+        return r;
+    }
+    double r[8];
+    for (int k = 0; k < 8; ++k) r[k] = a[k];
+    int i = 8;
+    for (; i < n - (n % 8); i += 8)
+        for (int k = 0; k < 8; ++k) r[k] = __dadd_rn(r[k], a[i + k]);
+    double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                           __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+    for (; i < n; ++i) res = __dadd_rn(res, a[i]);
+    return res;
+}
+
+// ---- state tensor (super_grid_rl.py:305-341) ------------------------------------------------------
+// [pos_0 .. pos_{N-1} | one merged plane with use_scanning] [observed obstacles] [free = NOT covered]
+// [distance channel], each W x L float32, y fastest.
+__device__ void write_state(const SuperParams& p, SuperSmem& sm, const uint16_t* dbuf, int e,
+                            const uint32_t* cov, const uint32_t* seen) {
+    const int N = p.N, W = p.g.W, L = p.g.L, Wp = p.g.Wp;
+    const int WL = W * L, pitch = p.dt_pitch;
+    const int npos = p.use_scanning ? 1 : N;
+    const int any_zero = sm.any_zero, dmax = sm.dmax;
+    const bool flat_one = sm.covered == 0;                   // nothing covered: channel is all 1
+    float* obs_e = p.obs + (size_t)e * p.C * WL;
+    if (p.vec_ok) {
+        const int Lq = L >> 2, qp = WL >> 2;
+        float4* dst = reinterpret_cast<float4*>(obs_e);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int nz = npos * qp;
+        for (int q = threadIdx.x; q < nz; q += ST) __stcs(dst + q, z4);
+        float4* d_obst = dst + (size_t)npos * qp;
+        float4* d_free = d_obst + qp;
+        float4* d_dist = d_free + qp;
+        int x = threadIdx.x / Lq, yq = threadIdx.x - x * Lq;
+        const int dx = ST / Lq, dyq = ST - dx * Lq;
+        for (int q = threadIdx.x; q < qp; q += ST) {
+            const int w = (yq >> 3) * Wp + x, nib = (yq & 7) * 4;
+            const uint32_t so = seen[w], cv = cov[w];
+            __stcs(d_obst + q, sm.lut[(so >> nib) & 15u]);
+            __stcs(d_free + q, sm.lut[(~cv >> nib) & 15u]);
+            float4 dv;
+            if (flat_one) {
+                dv = make_float4(1.f, 1.f, 1.f, 1.f);
+            } else {
+                const uint32_t* dp = reinterpret_cast<const uint32_t*>(dbuf + (size_t)x * pitch + 4 * yq);
+                const uint32_t a = dp[0], b = dp[1];
+                dv.x = dist_value((int)(a & 0xffffu), any_zero, dmax);
+                dv.y = dist_value((int)(a >> 16), any_zero, dmax);
+                dv.z = dist_value((int)(b & 0xffffu), any_zero, dmax);
+                dv.w = dist_value((int)(b >> 16), any_zero, dmax);
+            }
+            __stcs(d_dist + q, dv);
+            x += dx;
+            yq += dyq;
+            if (yq >= Lq) { yq -= Lq; ++x; }
+        }
+        __syncthreads();                                     // zero fill is ordered before the 1.0 patches
+        if (threadIdx.x < N) {
+            const uint32_t pv = sm.pos[threadIdx.x];
+            const int plane = p.use_scanning ? 0 : threadIdx.x;
+            obs_e[(size_t)plane * WL + unpack_x(pv) * L + unpack_y(pv)] = 1.0f;
+        }
+    } else {
+        // generic path (L not a multiple of 4 or unaligned buffer): one float per thread
+        const int total = p.C * WL;
+        for (int k = threadIdx.x; k < total; k += ST) {
+            const int c = k / WL, rem = k - c * WL;
+            const int x = rem / L, y = rem - x * L;
+            float v;
+            if (c < npos) {
+                v = 0.0f;
+                if (p.use_scanning) {
+                    for (int j = 0; j < N; ++j) v = (sm.pos[j] == pack_xy(x, y)) ? 1.0f : v;
+                } else {
+                    v = (sm.pos[c] == pack_xy(x, y)) ? 1.0f : 0.0f;
+                }
+            } else {
+                const int w = (y >> 5) * Wp + x, b = y & 31;
+                if (c == npos) v = (float)((seen[w] >> b) & 1u);
+                else if (c == npos + 1) v = (float)((~cov[w] >> b) & 1u);
+                else v = flat_one ? 1.0f : dist_value((int)dbuf[(size_t)x * pitch + y], any_zero, dmax);
+            }
+            __stcs(obs_e + k, v);
+        }
+    }
+}
+
+// One pass over env e in `mode`.  Returns true when the env finished and must be re-seeded in place
+// by a second (MODE_RESET) pass of the same CTA (fused auto-reset).
+__device__ bool super_pass(const SuperParams& p, SuperSmem& sm, uint16_t* dbuf, const int e, const int mode) {
+    const int N = p.N, R = p.R, S = 2 * R + 1;
+    const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
+    EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
+    uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
+    int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
+    uint32_t* cov = p.covered + (size_t)e * PW;
+    uint32_t* seen = p.seen_obst + (size_t)e * PW;
+    const bool fresh = (mode == MODE_RESET);
+
+    __syncthreads();                                         // previous pass is done with shared memory
+    if (fresh) {
+        // super_grid_rl.py:343-399: new map, new poses, nothing covered, nothing sensed
+        if (threadIdx.x == 0) {
+            int mi = 0;
+            draw_starts(p.wall, p.g, N, p.n_maps, p.map_idx_in, p.start_xy_in, p.seed,
+                        (uint32_t)(p.env_id_base + e), e, head->episode, sm.pos, &mi);
+            head->currstep = 0;
+            head->map_idx = mi;
+            head->episode = head->episode + 1;
+            head->ep_return = 0.0;
+            hcov[0] = 0;
+            for (int j = 0; j < N; ++j) hpos[j] = sm.pos[j];
+            p.needs_reset[e] = 0;
+            sm.covered = 0;
+        }
+        uint4* zc = reinterpret_cast<uint4*>(cov);
+        uint4* zs = reinterpret_cast<uint4*>(seen);
+        for (int k = threadIdx.x; k < PW / 4; k += ST) {
+            zc[k] = make_uint4(0, 0, 0, 0);
+            zs[k] = make_uint4(0, 0, 0, 0);
+        }
+    }
+    bool sentinel = false;
+    if (mode == MODE_STEP && p.act_fmt == MCOV_ACT_I64_BASE4)
+        sentinel = (reinterpret_cast<const long long*>(p.actions)[e] == -1);
+    const bool dyn = (mode == MODE_STEP) && !sentinel;
+    if (dyn && p.dist_reward) l1_transform(cov, p.g, dbuf, p.dt_pitch, sm);   // start-of-step map (:117-118)
+
+    if (warp == 0 && !fresh) {
+        const int map_idx = head->map_idx;
+        const uint32_t* wall = p.wall + (size_t)map_idx * PW;
+        const uint32_t* tpos = p.pos + (size_t)map_idx * PW;
+        const uint32_t myv = lane < N ? hpos[lane] : 0xffffffffu;
+        uint32_t pv = myv;
+        if (dyn) {
+            // ---- action decode (:92-100): digit c of the joint action drives control slot c ----
+            int u = 0;
+            if (p.act_fmt == MCOV_ACT_I64_BASE4)
+                u = (int)((reinterpret_cast<const long long*>(p.actions)[e] >> (2 * lane)) & 3);
+            else if (lane < N)
+                u = (int)(reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * N + lane] & 3u);
+            // ---- scan order (:107-111,125-129): control c goes to the c-th robot in raster order of
+            // the start-of-step poses (key x + y*W, ties by index)
+            int rank = lane, zc = lane;
+            if (p.use_scanning) {
+                const int key = unpack_x(myv) + unpack_y(myv) * W;
+                rank = 0;
+                for (int j = 0; j < N; ++j) {
+                    const int kj = __shfl_sync(FULL, key, j);
+                    rank += (kj < key) || (kj == key && j < lane);
+                }
+                for (int j = 0; j < N; ++j)
+                    if (__shfl_sync(FULL, rank, j) == lane) zc = j;
+            }
+            // ---- sequential, collision-checked moves (:121-174).  Super table: 0:x-1 1:x+1 2:y+1 3:y-1.
+            // A robot moves only on its own turn, so control c's target is known up front.
+            const uint32_t pz = __shfl_sync(FULL, myv, zc & 31);
+            const int tx = unpack_x(pz) + (u == 1) - (u == 0);
+            const int ty = unpack_y(pz) + (u == 2) - (u == 3);
+            int blocked0 = 1;
+            if (lane < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
+            const uint32_t tv = pack_xy(tx, ty);
+            int moved = 0, ncoll = 0;
+            for (int c = 0; c < N; ++c) {
+                const uint32_t tvc = __shfl_sync(FULL, tv, c);
+                const int blk = __shfl_sync(FULL, blocked0, c);
+                const int z = __shfl_sync(FULL, zc, c);
+                const uint32_t b = __ballot_sync(FULL, lane < N && pv == tvc);
+                if (!blk && b == 0u) {
+                    if (lane == z) pv = tvc;
+                    if (lane == c) moved = 1;
+                } else {
+                    ++ncoll;
+                }
+            }
+            // per-slot reward so far: -collision_penalty, or the start-of-step distance value (:138-139)
+            double rc = 0.0;
+            if (lane < N) {
+                if (!moved) rc = 0.0 - p.cp;
+                else if (p.dist_reward)
+                    rc = 0.0 + (double)dist_value((int)dbuf[(size_t)tx * p.dt_pitch + ty], sm.any_zero, sm.dmax);
+            }
+            // robot i accumulates onto the slot that drove it (r2c, :129)
+            const double racc0_lo = rc;
+            const int hi32 = __shfl_sync(FULL, __double2hiint(racc0_lo), rank & 31);
+            const int lo32 = __shfl_sync(FULL, __double2loint(racc0_lo), rank & 31);
+            double racc = __hiloint2double(hi32, lo32);
+
+            // ---- footprints (:176-201), robots in index order, lanes = footprint rows -------------
+            const int lastbits = L & 31;
+            int cnt_new = 0;
+            for (int i = 0; i < N; ++i) {
+                const uint32_t pi = __shfl_sync(FULL, pv, i);
+                const int xi = unpack_x(pi), yi = unpack_y(pi);
+                const int x = xi - R + lane;
+                uint32_t rel_new = 0, rel_al = 0;
+                if (lane < S && x >= 0 && x < W) {
+                    const int y0 = yi - R, s0 = y0 >> 5, sh = y0 & 31;
+                    const uint64_t m64 = (uint64_t)low_mask(S) << sh;
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        const int s = s0 + k;
+                        uint32_t m = k ? (uint32_t)(m64 >> 32) : (uint32_t)m64;
+                        if (s == strips - 1 && lastbits) m &= low_mask(lastbits);
+                        if (!m || s < 0 || s >= strips) continue;
+                        const int w = s * Wp + x;
+                        const uint32_t wl = __ldg(wall + w) & m, walk = ~__ldg(wall + w) & m;
+                        const uint32_t worth = __ldg(tpos + w) & m;
+                        const uint32_t c0 = cov[w], so = seen[w];
+                        const uint32_t nf = walk & ~c0, al = walk & c0;
+                        if (nf) cov[w] = c0 | nf;
+                        if (wl & ~so) seen[w] = so | wl;
+                        cnt_new += __popc(nf);
+                        const uint32_t nfw = nf & worth;
+                        rel_new |= k ? (nfw << (32 - sh)) : (nfw >> sh);
+                        rel_al |= k ? (al << (32 - sh)) : (al >> sh);
+                    }
+                }
+                if (lane < S) sm.rows[i * S + lane] = make_uint2(rel_new, rel_al);
+                __syncwarp();
+            }
+            // float64 accumulation in the reference's raster order (x rows outer, y inner)
+            if (lane < N) {
+                for (int r = 0; r < S; ++r) {
+                    const uint2 rb = sm.rows[lane * S + r];
+                    uint32_t both = rb.x | rb.y;
+                    while (both) {
+                        const uint32_t bit = both & (0u - both);
+                        both ^= bit;
+                        if (rb.x & bit) racc = __dadd_rn(racc, 1.0);                 // += grid[j][k]
+                        else racc = __dsub_rn(racc, p.free_penalty);                 // -= free_penalty
+                    }
+                }
+                // motion_penalty quirk (:203-208): -1 per slot on the very first step
+                if (head->flags & 1u) racc = __dadd_rn(racc, -1.0);
+                sm.rew[rank] = racc;
+            }
+            cnt_new = (int)__reduce_add_sync(FULL, cnt_new);
+            __syncwarp();
+            if (lane < N && pv != myv) hpos[lane] = pv;
+            if (lane == 0) {
+                double r = numpy_sum(sm.rew, N);                                    // :214
+                const int cs = head->currstep + 1;                                  // :211
+                const int covered = hcov[0] + cnt_new;
+                const int fc = __ldg(p.free_counts + map_idx);
+                double th = head->done_thresh;
+                int dn = 0;
+                bool full;                                                         // :215, :401-414
+                if (th >= 1.0) full = covered >= fc;
+                else full = th <= (double)covered / (double)fc;
+                if (full) { r += p.terminal; th += p.done_incr; dn = 1; head->done_thresh = th; }
+                const double epr = head->ep_return + r;
+                head->currstep = cs;
+                head->flags = head->flags & ~1u;
+                head->ep_return = epr;
+                if (cnt_new) hcov[0] = covered;
+                sm.covered = covered;
+                const bool trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
+                sm.stats[4] += (double)ncoll;
+                sm.stats[5] += (double)cnt_new;
+                sm.stats[6] += (double)N;
+                int nr = 0;
+                if (dn || trunc) {
+                    sm.stats[0] += 1.0;
+                    sm.stats[1] += epr;
+                    sm.stats[2] += (double)cs;
+                    sm.stats[3] += (double)covered / (double)fc;
+                    nr = 1;
+                }
+                p.reward[e] = (float)r;
+                if (p.reward64) p.reward64[e] = r;
+                p.done[e] = (uint8_t)dn;
+                sm.again = (nr && p.auto_reset) ? 1 : 0;
+                p.needs_reset[e] = (nr && !p.auto_reset) ? 1 : 0;
+            }
+        } else if (lane == 0) {
+            sm.covered = hcov[0];
+            sm.again = 0;
+            if (mode == MODE_STEP) {                                               // sentinel (:88-90)
+                p.reward[e] = 0.0f;
+                if (p.reward64) p.reward64[e] = 0.0;
+                p.done[e] = 1;
+                sm.again = p.auto_reset ? 1 : 0;
+                p.needs_reset[e] = p.auto_reset ? 0 : 1;
+            }
+        }
+        if (lane < N) sm.pos[lane] = pv;
+    } else if (fresh && threadIdx.x == 0) {
+        sm.again = 0;
+    }
+    __syncthreads();
+    if (sm.again) return true;                                // state comes from the reset pass
+
+    if (sm.covered > 0) {
+        l1_transform(cov, p.g, dbuf, p.dt_pitch, sm);
+    } else if (threadIdx.x == 0) {
+        sm.any_zero = 1;
+        sm.dmax = 0;
+    }
+    __syncthreads();
+    write_state(p, sm, dbuf, e, cov, seen);
+    return false;
+}
+
+__global__ void __launch_bounds__(ST)
+super_env_kernel(const SuperParams p, const int dt_cells) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ SuperSmem sm;
+    uint16_t* dbuf = p.dt_scratch ? p.dt_scratch + (size_t)blockIdx.x * dt_cells
+                                  : reinterpret_cast<uint16_t*>(smem_raw);
+    if (threadIdx.x < 16) {
+        const uint32_t t = threadIdx.x;
+        sm.lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
+                                (t & 8u) ? 1.0f : 0.0f);
+    }
+    if (threadIdx.x < MCOV_STATS_LEN) sm.stats[threadIdx.x] = 0.0;
+    __syncthreads();
+
+    for (int e = blockIdx.x; e < p.E; e += gridDim.x) {
+        int m = p.mode;
+        if (m == MODE_RESET) {
+            int act = 1;
+            if (p.mask) act = p.mask[e];
+            else if (p.mask_from_flags) act = p.needs_reset[e];
+            if (!act) continue;                               // CTA-uniform
+        }
+        while (super_pass(p, sm, dbuf, e, m)) m = MODE_RESET; // fused auto-reset
+    }
+
+    // ---- episode statistics: CTA row -> last CTA folds all rows (single launch) -------------------
+    if (p.stats_out) {
+        __syncthreads();
+        if (threadIdx.x < MCOV_STATS_LEN)
+            p.stats_partial[(size_t)blockIdx.x * MCOV_STATS_LEN + threadIdx.x] = sm.stats[threadIdx.x];
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) sm.last = (atomicAdd(p.counter, 1u) == gridDim.x - 1) ? 1 : 0;
+        __syncthreads();
+        if (sm.last) {
+            __threadfence();
+            if (threadIdx.x < MCOV_STATS_LEN) {
+                double s = 0.0;
+                for (int r = 0; r < (int)gridDim.x; ++r)
+                    s += __ldcg(p.stats_partial + (size_t)r * MCOV_STATS_LEN + threadIdx.x);
+                p.stats_out[threadIdx.x] = s;
+            }
+            if (threadIdx.x == 0) *p.counter = 0u;
+        }
+    }
+}
+
+// uint16 elements per x row of the distance work buffer: 2 * (odd number of 32-bit words)
+inline int dt_pitch_of(const Geometry& g) {
+    int words = g.strips * 16;
+    if ((words & 1) == 0) words += 1;
+    return 2 * words;
+}
+
+struct SuperShape {
+    int grid, pitch, cells;
+    size_t smem;                 // dynamic shared memory (0 when the work buffer is global)
+    bool global_dt;
+};
+
+inline SuperShape super_shape(const mcov_env* env) {
+    SuperShape s;
+    s.pitch = dt_pitch_of(env->g);
+    s.cells = env->g.W * s.pitch;
+    const size_t bytes = (size_t)s.cells * 2;
+    s.global_dt = bytes > 200 * 1024;
+    s.smem = s.global_dt ? 0 : ((bytes + 15) / 16 * 16);
+    int per_sm = 4;
+    if (!s.global_dt) {
+        const int by_smem = (int)((220 * 1024) / (s.smem + sizeof(SuperSmem) + 1024));
+        if (per_sm > by_smem) per_sm = by_smem;
+        if (per_sm < 1) per_sm = 1;
+    } else {
+        per_sm = 2;
+    }
+    int grid = env->num_sms * per_sm;
+    if (grid > env->cfg.num_envs) grid = env->cfg.num_envs;
+    s.grid = grid;
+    return s;
+}
+
+}  // namespace
+
+int super_grid_size(const mcov_env* env) { return super_shape(env).grid; }
+
+int64_t super_dt_scratch_bytes(const mcov_env* env) {
+    const SuperShape s = super_shape(env);
+    return s.global_dt ? (int64_t)s.grid * s.cells * 2 : 0;
+}
+
+cudaError_t launch_super(mcov_env* env, SuperParams& p, cudaStream_t st) {
+    const SuperShape s = super_shape(env);
+    p.dt_pitch = s.pitch;
+    if (s.global_dt && !p.dt_scratch) return cudaErrorInvalidValue;
+    if (!s.global_dt) p.dt_scratch = nullptr;
+    if (s.smem > 40 * 1024) {
+        cudaError_t err = cudaFuncSetAttribute(super_env_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)s.smem);
+        if (err != cudaSuccess) return err;
+    }
+    super_env_kernel<<<s.grid, ST, s.smem, st>>>(p, s.cells);
+    env->launches++;
+    return cudaGetLastError();
+}
+
 }  // namespace mcov

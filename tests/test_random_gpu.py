@@ -1,0 +1,121 @@
+"""Randomised parity: small random maps / configs, oracle vs the CUDA env, bit-exact.
+
+Covers what the golden fixtures cannot enumerate: map sizes that are not multiples of 4 or 32
+(generic store path, strip tails), all-free and nearly-blocked maps, N up to 16, radii up to the
+window limit, per-robot uint8 actions, many envs with different maps/poses in one launch."""
+import numpy as np
+import pytest
+
+from oracle import coverage_oracle as oc
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_map(rng, W, L, p_obst):
+    g = np.where(rng.random((W, L)) < p_obst, -1.0, 1.0)
+    free = np.argwhere(g > 0)
+    if len(free) < 20:                       # keep enough room for the robots
+        g[:] = 1.0
+    return g
+
+
+def _dec_cfg(rng, N):
+    lidar = rng.random() < 0.4
+    R = int(rng.integers(1, 7 if lidar else 5))
+    cfg = dict(numrobot=N, maxsteps=int(rng.integers(20, 60)), collision_penalty=float(rng.integers(0, 6)),
+               done_thresh=float(rng.choice([0.2, 0.6, 1.0, 1.5])), done_incr=float(rng.choice([0.0, 0.1])),
+               terminal_reward=float(rng.integers(0, 40)), dist_reward=0, train_maxsteps=1000,
+               test_maxsteps=1000, egoradius=int(rng.integers(1, 8)), mini_map_rad=0,
+               comm_radius=int(rng.integers(0, 6)), allow_comm=1, map_sharing=int(rng.random() < 0.3),
+               single_square_tool=int(rng.random() < 0.2), dijkstra_input=0)
+    if lidar:
+        cfg.update(sensor_type="lidar", sensor_config={"range": R, "num_lasers": int(rng.choice([5, 9, 21, 33]))})
+    else:
+        cfg.update(sensor_type="square_sensor", sensor_config={"range": R})
+    return cfg
+
+
+def _super_cfg(rng, N):
+    return dict(numrobot=N, train_maxsteps=1000, test_maxsteps=1000,
+                collision_penalty=float(rng.integers(0, 6)), senseradius=int(rng.integers(0, 5)),
+                free_penalty=float(rng.choice([0.0, 0.2, 0.37, 1.0])),
+                done_thresh=float(rng.choice([0.3, 0.7, 1.0])), done_incr=float(rng.choice([0.0, 0.05])),
+                terminal_reward=float(rng.integers(0, 40)), dist_reward=int(rng.random() < 0.4),
+                use_scanning=int(rng.random() < 0.4))
+
+
+def _run_case(kind, seed, E=9, T=40):
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL
+    rng = np.random.default_rng(seed)
+    W, L = int(rng.integers(6, 45)), int(rng.integers(6, 45))
+    if seed % 3 == 0:
+        L = (L // 4) * 4 + 4                 # exercise the vectorised store path too
+    N = int(rng.integers(1, 9 if kind == "dec" else 17))
+    grids = [_rand_map(rng, W, L, float(rng.choice([0.0, 0.1, 0.3]))) for _ in range(3)]
+    cfg = _dec_cfg(rng, N) if kind == "dec" else _super_cfg(rng, N)
+    np.random.seed(seed)
+    mk = (lambda: oc.OracleDecGridRL(grids, cfg, use_graph=True)) if kind == "dec" else \
+         (lambda: oc.OracleSuperGridRL(grids, cfg))
+    oracles = [mk() for _ in range(E)]
+    cls = VecDecGridRL if kind == "dec" else VecSuperGridRL
+    vec = cls(grids, cfg, num_envs=E, device="cuda:0")
+
+    def reset_all(which):
+        maps = np.zeros((E,), np.int32)
+        start = np.zeros((E, N, 2), np.int16)
+        mask = np.zeros((E,), np.uint8)
+        outs = {}
+        for e in which:
+            o = oracles[e]
+            mi = int(rng.integers(len(grids)))
+            o.reset(False, None, map_index=mi)               # draws poses from np.random
+            maps[e], mask[e] = mi, 1
+            start[e, :, 0], start[e, :, 1] = o._xinds, o._yinds
+            outs[e] = o.reset(False, None, start_xy=start[e], map_index=mi)[0]
+        obs = vec.reset(map_idx=maps, start_xy=start, mask=mask)
+        for e in which:
+            ref = outs[e] if kind == "dec" else outs[e][0]
+            assert np.array_equal(obs[e].cpu().numpy(), np.asarray(ref, dtype=np.float32)), \
+                "seed %d reset obs env %d" % (seed, e)
+
+    reset_all(range(E))
+    for t in range(T):
+        act = rng.integers(0, 4, size=(E, N)).astype(np.uint8)
+        obs, rew, done = vec.step(torch.from_numpy(act))
+        r64 = vec.reward64.cpu().numpy()
+        dn = done.cpu().numpy()
+        ob = obs.cpu().numpy()
+        pos = vec.positions().cpu().numpy()
+        pct = vec.percent_covered().cpu().numpy()
+        finished = []
+        for e, o in enumerate(oracles):
+            oo, orr, od = o.step(act[e].astype(np.int64))
+            tag = "seed %d step %d env %d (%s W=%d L=%d N=%d cfg=%s)" % (seed, t, e, kind, W, L, N, cfg)
+            if kind == "dec":
+                oo = oo[0] if isinstance(oo, list) else oo
+                assert np.array_equal(ob[e], oo.astype(np.float32)), "obs " + tag
+            else:
+                assert np.array_equal(ob[e], oo[0].astype(np.float32)), "state " + tag
+            assert np.array_equal(pos[e, :, 0], o._xinds) and np.array_equal(pos[e, :, 1], o._yinds), "pos " + tag
+            assert float(r64[e]) == float(orr), "reward %r vs %r %s" % (r64[e], orr, tag)
+            assert bool(dn[e]) == bool(od), "done " + tag
+            assert float(pct[e]) == float(o.percent_covered()), "pct " + tag
+            if od:
+                finished.append(e)
+        if kind == "dec":
+            adj = vec.adjacency()
+            for e, o in enumerate(oracles):
+                assert np.array_equal(adj[e], o._adjacency_matrix), "adjacency seed %d" % seed
+        if finished:
+            reset_all(finished)
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_dec_random_vs_oracle(seed):
+    _run_case("dec", 1000 + seed)
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_super_random_vs_oracle(seed):
+    _run_case("super", 2000 + seed)
