@@ -94,6 +94,7 @@ unsigned char* scratch_moves(const mcov_env* env) {
 unsigned char* scratch_super_dt(const mcov_env* env) {
     return scratch_moves(env) + align_up64((int64_t)env->cfg.num_envs * 8, 256);
 }
+unsigned char* scratch_extras(const mcov_env* env) { return scratch_super_dt(env); }   // Dec: same slot
 
 int check_ready(const mcov_env* env) {
     if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
@@ -322,6 +323,7 @@ int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_d
     off = align_up64(off + E * 4, 256);
     off = align_up64(off + E * 8, 256);
     if (c.env_type == MCOV_ENV_SUPER) off = align_up64(off + mcov::super_dt_scratch_bytes(env), 256);
+    else off = align_up64(off + mcov::dec_extras_scratch_bytes(env), 256);
     l.total_bytes = off;
     return MCOV_OK;
 }
@@ -414,14 +416,14 @@ static int run_dec(mcov_env* env, int mode, const void* actions, int act_fmt, co
         ce = mcov::launch_dec(env, p, st);
         if (ce != cudaSuccess) return cuda_fail(ce, "dec move launch");
         p.dist_term = reinterpret_cast<float*>(scratch_dist_term(env));
-        ce = mcov::launch_dec_extras(env, nullptr, 1, st);
+        ce = mcov::launch_dec_extras(env, nullptr, p.dist_term, scratch_extras(env), 1, st);
         if (ce != cudaSuccess) return cuda_fail(ce, "dec dist-term launch");
         p.phases = mcov::PH_SENSE;
     }
     ce = mcov::launch_dec(env, p, st);
     if (ce != cudaSuccess) return cuda_fail(ce, "dec kernel launch");
     if (extras) {
-        ce = mcov::launch_dec_extras(env, obs, 0, st);
+        ce = mcov::launch_dec_extras(env, obs, nullptr, scratch_extras(env), 0, st);
         if (ce != cudaSuccess) return cuda_fail(ce, "dec extras launch");
     }
     return MCOV_OK;

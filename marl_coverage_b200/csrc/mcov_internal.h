@@ -127,7 +127,9 @@ struct mcov_env {
 namespace mcov {
 cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st);
 cudaError_t launch_dec_share(mcov_env* env, cudaStream_t st);
-cudaError_t launch_dec_extras(mcov_env* env, float* obs, int pre_sense, cudaStream_t st);
+cudaError_t launch_dec_extras(mcov_env* env, float* obs, float* dist_term, unsigned char* scratch,
+                              int pre_sense, cudaStream_t st);
+int64_t dec_extras_scratch_bytes(const mcov_env* env);  // 0 when the work area lives in shared memory
 cudaError_t launch_super(mcov_env* env, SuperParams& p, cudaStream_t st);
 cudaError_t launch_stats_reduce(mcov_env* env, const double* partial, int rows, double* out,
                                 cudaStream_t st);

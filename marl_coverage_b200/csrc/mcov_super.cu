@@ -20,6 +20,7 @@
 // streaming stores straight into the torch buffer.  Finished envs are re-seeded by the same CTA in
 // the same launch (fused auto-reset); episode statistics are folded by the last CTA.
 #include "mcov_internal.h"
+#include "mcov_dt.cuh"
 
 namespace mcov {
 
@@ -27,7 +28,6 @@ namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int ST = 512;                       // threads per CTA
-constexpr int DINF = 0xffff;                  // "no zero pixel in reach" (> W + L for any int16 map)
 constexpr int MAXS = 2 * MCOV_MAX_RADIUS + 1;
 
 struct SuperSmem {
@@ -37,98 +37,20 @@ struct SuperSmem {
     uint2 rows[MCOV_MAX_ROBOTS * MAXS];       // per (robot, footprint row): .x new cells worth 1, .y re-covered
     uint32_t pos[MCOV_MAX_ROBOTS];            // poses after the moves
     int any_zero, dmax, covered, again, skip, last;
+    int red[2];
 };
 
-// ---- exact L1 distance transform -----------------------------------------------------------------
-// d[x][y] = taxicab distance from (x, y) to the nearest NOT-covered in-map cell (0 on such cells),
-// what cv2.distanceTransform(DIST_L1, DIST_MASK_PRECISE) returns at super_grid_rl.py:295.
-// Pass 1 runs along y in closed form on the bit words; pass 2 is the min-plus sweep along x.
-// Layout: uint16 d[x * pitch + y], pitch = 2 * (odd word count) so that both passes and the state
-// writer touch consecutive shared-memory banks.
-__device__ void l1_transform(const uint32_t* cov, const Geometry& g, uint16_t* d, int pitch,
-                             SuperSmem& sm) {
-    const int W = g.W, L = g.L, Wp = g.Wp, strips = g.strips;
-    const int lastbits = L & 31;
-    if (threadIdx.x == 0) { sm.any_zero = 0; sm.dmax = 0; }
-    __syncthreads();
-    int anyz = 0;
-    const int nw = W * strips;
-    for (int idx = threadIdx.x; idx < nw; idx += blockDim.x) {
-        const int s = idx / W, x = idx - s * W;              // x fastest within a strip
-        auto zero_word = [&](int ss) -> uint32_t {
+// Distance transform of the covered plane: zero pixels are the NOT-covered in-map cells
+// (obstacles included) — super_grid_rl.py:292-295.
+__device__ void super_transform(const uint32_t* cov, const Geometry& g, uint16_t* d, int pitch, SuperSmem& sm) {
+    const int Wp = g.Wp, strips = g.strips, lastbits = g.L & 31;
+    const DtResult r = l1_transform(
+        [&](int ss, int x) -> uint32_t {
             const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
             return ~cov[ss * Wp + x] & valid;
-        };
-        const uint32_t z = zero_word(s);
-        anyz |= (z != 0u);
-        int base_lo = DINF, base_hi = DINF;                  // gap to the nearest zero pixel in other strips
-        for (int ss = s - 1; ss >= 0; --ss) {
-            const uint32_t t = zero_word(ss);
-            if (t) { base_lo = 32 * (s - ss) - (31 - __clz(t)); break; }
-        }
-        for (int ss = s + 1; ss < strips; ++ss) {
-            const uint32_t t = zero_word(ss);
-            if (t) { base_hi = 32 * (ss - s) + (__ffs(t) - 1) - 31; break; }
-        }
-        uint32_t* drow = reinterpret_cast<uint32_t*>(d + (size_t)x * pitch + 32 * s);
-#pragma unroll 4
-        for (int j = 0; j < 16; ++j) {
-            uint32_t packed = 0;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int b = 2 * j + h;
-                const uint32_t mlo = z & (FULL >> (31 - b)), mhi = z & (FULL << b);
-                const int dl = mlo ? b - (31 - __clz(mlo)) : b + base_lo;
-                const int dh = mhi ? (__ffs(mhi) - 1) - b : (31 - b) + base_hi;
-                const int v = min(min(dl, dh), DINF);
-                packed |= (uint32_t)v << (16 * h);
-            }
-            drow[j] = packed;
-        }
-    }
-    anyz = __syncthreads_or(anyz);
-    int mx = 0;
-    for (int y = threadIdx.x; y < L; y += blockDim.x) {
-        uint16_t* col = d + y;
-        int v = DINF;
-        for (int x0 = 0; x0 < W; x0 += 8) {
-            int t[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = (x0 + k < W) ? (int)col[(size_t)(x0 + k) * pitch] : DINF;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                v = min(t[k], v + 1);
-                v = min(v, DINF);
-                if (x0 + k < W) col[(size_t)(x0 + k) * pitch] = (uint16_t)v;
-            }
-        }
-        v = DINF;
-        for (int x0 = W - 1; x0 >= 0; x0 -= 8) {
-            int t[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = (x0 - k >= 0) ? (int)col[(size_t)(x0 - k) * pitch] : DINF;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                if (x0 - k >= 0) {
-                    v = min(t[k], v + 1);
-                    v = min(v, DINF);
-                    col[(size_t)(x0 - k) * pitch] = (uint16_t)v;
-                    mx = max(mx, v);
-                }
-            }
-        }
-    }
-    mx = __reduce_max_sync(FULL, mx);
-    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(&sm.dmax, mx);
-    if (threadIdx.x == 0) sm.any_zero = anyz;
+        }, g, d, pitch, sm.red);
+    if (threadIdx.x == 0) { sm.any_zero = r.any_zero; sm.dmax = r.dmax; }
     __syncthreads();
-}
-
-// float32 value of the distance channel: 1 - d / max(d)  (super_grid_rl.py:297-303, all float32)
-__device__ __forceinline__ float dist_value(int dv, int any_zero, int dmax) {
-    if (!any_zero) return 0.0f;                               // cv2: FLT_MAX everywhere -> 1 - 1
-    if (dmax <= 0) return 1.0f;                               // nothing covered yet: no division
-    return __fsub_rn(1.0f, __fdiv_rn((float)dv, (float)dmax));
 }
 
 // np.sum of a float64 vector the way numpy adds it (pairwise_sum with 8 accumulators for n >= 8;
@@ -265,7 +187,7 @@ __device__ bool super_pass(const SuperParams& p, SuperSmem& sm, uint16_t* dbuf, 
     if (mode == MODE_STEP && p.act_fmt == MCOV_ACT_I64_BASE4)
         sentinel = (reinterpret_cast<const long long*>(p.actions)[e] == -1);
     const bool dyn = (mode == MODE_STEP) && !sentinel;
-    if (dyn && p.dist_reward) l1_transform(cov, p.g, dbuf, p.dt_pitch, sm);   // start-of-step map (:117-118)
+    if (dyn && p.dist_reward) super_transform(cov, p.g, dbuf, p.dt_pitch, sm);   // start-of-step map (:117-118)
 
     if (warp == 0 && !fresh) {
         const int map_idx = head->map_idx;
@@ -433,7 +355,7 @@ __device__ bool super_pass(const SuperParams& p, SuperSmem& sm, uint16_t* dbuf, 
     if (sm.again) return true;                                // state comes from the reset pass
 
     if (sm.covered > 0) {
-        l1_transform(cov, p.g, dbuf, p.dt_pitch, sm);
+        super_transform(cov, p.g, dbuf, p.dt_pitch, sm);
     } else if (threadIdx.x == 0) {
         sm.any_zero = 1;
         sm.dmax = 0;
@@ -488,13 +410,6 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
             if (threadIdx.x == 0) *p.counter = 0u;
         }
     }
-}
-
-// uint16 elements per x row of the distance work buffer: 2 * (odd number of 32-bit words)
-inline int dt_pitch_of(const Geometry& g) {
-    int words = g.strips * 16;
-    if ((words & 1) == 0) words += 1;
-    return 2 * words;
 }
 
 struct SuperShape {

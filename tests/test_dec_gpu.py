@@ -12,11 +12,6 @@ from oracle.trace import Trace
 pytestmark = pytest.mark.gpu
 
 
-def _supported(tr):
-    c = tr.config
-    return not (c["dist_reward"] or c["dijkstra_input"] or c["mini_map_rad"] > 0)
-
-
 DEC_TRACES = [n for n in golden_names("dec")]
 
 
@@ -25,8 +20,6 @@ def test_dec_golden_single_env(name):
     from marl_coverage_b200 import VecDecGridRL
     from gpu_helpers import replay_trace_on_gpu
     tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
-    if not _supported(tr):
-        pytest.skip("gated observation layers not built yet")
     tol = 1e-6 if tr.config["mini_map_rad"] > 0 else 0.0
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=1, check_envs=(0,), obs_tol=tol)
 

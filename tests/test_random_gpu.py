@@ -24,10 +24,11 @@ def _dec_cfg(rng, N):
     R = int(rng.integers(1, 7 if lidar else 5))
     cfg = dict(numrobot=N, maxsteps=int(rng.integers(20, 60)), collision_penalty=float(rng.integers(0, 6)),
                done_thresh=float(rng.choice([0.2, 0.6, 1.0, 1.5])), done_incr=float(rng.choice([0.0, 0.1])),
-               terminal_reward=float(rng.integers(0, 40)), dist_reward=0, train_maxsteps=1000,
-               test_maxsteps=1000, egoradius=int(rng.integers(1, 8)), mini_map_rad=0,
+               terminal_reward=float(rng.integers(0, 40)), dist_reward=int(rng.random() < 0.3),
+               train_maxsteps=1000, test_maxsteps=1000, egoradius=int(rng.integers(1, 8)),
+               mini_map_rad=int(rng.integers(1, 11)) if rng.random() < 0.2 else 0,
                comm_radius=int(rng.integers(0, 6)), allow_comm=1, map_sharing=int(rng.random() < 0.3),
-               single_square_tool=int(rng.random() < 0.2), dijkstra_input=0)
+               single_square_tool=int(rng.random() < 0.2), dijkstra_input=int(rng.random() < 0.25))
     if lidar:
         cfg.update(sensor_type="lidar", sensor_config={"range": R, "num_lasers": int(rng.choice([5, 9, 21, 33]))})
     else:
@@ -76,8 +77,12 @@ def _run_case(kind, seed, E=9, T=40):
         obs = vec.reset(map_idx=maps, start_xy=start, mask=mask)
         for e in which:
             ref = outs[e] if kind == "dec" else outs[e][0]
-            assert np.array_equal(obs[e].cpu().numpy(), np.asarray(ref, dtype=np.float32)), \
-                "seed %d reset obs env %d" % (seed, e)
+            got = obs[e].cpu().numpy()
+            if kind == "dec" and cfg["mini_map_rad"] > 0:
+                assert np.abs(got - np.asarray(ref, dtype=np.float32)).max() <= 1e-6
+            else:
+                assert np.array_equal(got, np.asarray(ref, dtype=np.float32)), \
+                    "seed %d reset obs env %d" % (seed, e)
 
     reset_all(range(E))
     for t in range(T):
@@ -94,7 +99,10 @@ def _run_case(kind, seed, E=9, T=40):
             tag = "seed %d step %d env %d (%s W=%d L=%d N=%d cfg=%s)" % (seed, t, e, kind, W, L, N, cfg)
             if kind == "dec":
                 oo = oo[0] if isinstance(oo, list) else oo
-                assert np.array_equal(ob[e], oo.astype(np.float32)), "obs " + tag
+                if cfg["mini_map_rad"] > 0:      # bilinear layers: 1e-6
+                    assert np.abs(ob[e] - oo.astype(np.float32)).max() <= 1e-6, "obs " + tag
+                else:
+                    assert np.array_equal(ob[e], oo.astype(np.float32)), "obs " + tag
             else:
                 assert np.array_equal(ob[e], oo[0].astype(np.float32)), "state " + tag
             assert np.array_equal(pos[e, :, 0], o._xinds) and np.array_equal(pos[e, :, 1], o._yinds), "pos " + tag
@@ -111,7 +119,7 @@ def _run_case(kind, seed, E=9, T=40):
             reset_all(finished)
 
 
-@pytest.mark.parametrize("seed", range(24))
+@pytest.mark.parametrize("seed", range(40))
 def test_dec_random_vs_oracle(seed):
     _run_case("dec", 1000 + seed)
 
