@@ -244,29 +244,15 @@ def gen_actions(torch, device, T, E, N, seed):
 def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, flush=None):
     """W untimed + K timed steps.  Returns (ms total over K by CUDA events, per-step ms list or None).
     With `flush` (a big tensor) the L2 is overwritten between steps and each step is timed alone."""
+    from marl_coverage_b200.sharding import StatsReducer
     dev = env.device
-    side = torch.cuda.Stream(device=dev) if world > 1 else None
-    ev_stats = [torch.cuda.Event() for _ in range(2)]
-    ev_red = [torch.cuda.Event() for _ in range(2)]
-    stats_bufs = [torch.zeros(8, dtype=torch.float64, device=dev) for _ in range(2)]
-    total_stats = torch.zeros(8, dtype=torch.float64, device=dev)
+    red = StatsReducer(dev, world=world)                 # NCCL SUM of the 64-byte statistics vector
     main = torch.cuda.current_stream(dev)
 
     def one(k):
-        b = k & 1
-        if side is not None and k >= 2:
-            main.wait_event(ev_red[b])                   # all-reduce of step k-2 has left this buffer
-        env.stats = stats_bufs[b]
+        env.stats = red.buffer()
         env.step(acts[k % acts.shape[0]], want_stats=True)
-        if side is not None:
-            ev_stats[b].record(main)
-            with torch.cuda.stream(side):
-                side.wait_event(ev_stats[b])
-                dist.all_reduce(stats_bufs[b])           # NCCL SUM of the 64-byte statistics vector
-                total_stats.add_(stats_bufs[b])
-                ev_red[b].record(side)
-        else:
-            total_stats.add_(stats_bufs[b])
+        red.submit()
 
     for k in range(warmup):
         one(k)
@@ -280,8 +266,8 @@ def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, f
         e0.record(main)
         for k in range(warmup, warmup + steps):
             one(k)
-        if side is not None:
-            main.wait_stream(side)
+        if world > 1:
+            main.wait_stream(red.side)
         e1.record(main)
         torch.cuda.synchronize(dev)
         ms = e0.elapsed_time(e1)
@@ -301,7 +287,8 @@ def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, f
     if world > 1:
         dist.barrier()
         torch.cuda.synchronize(dev)
-    return ms, per, total_stats
+    red.finish()
+    return ms, per, red.total
 
 
 def run_gpu(args):

@@ -1,0 +1,73 @@
+"""Host-side logic that needs no GPU: map supply, plane packing, action forms, lidar beam table,
+algorithmic-byte model of bench.py."""
+import numpy as np
+import pytest
+
+from marl_coverage_b200 import maps
+from marl_coverage_b200.action_spaces import Discrete
+from marl_coverage_b200.envs import _scalar_action
+from marl_coverage_b200.sensors import LidarSensor, SquareSensor, lidar_beam_table
+from oracle import coverage_oracle as oc
+
+
+def test_plane_pack_roundtrip():
+    rng = np.random.default_rng(0)
+    for W, L in ((1, 1), (5, 31), (7, 32), (9, 33), (102, 102), (64, 65)):
+        m = rng.random((W, L)) < 0.4
+        w = maps.pack_plane_host(m)
+        strips, Wp, PW = maps._geometry(W, L)
+        assert w.shape == (PW,) and Wp % 4 == 0
+        assert np.array_equal(maps.unpack_plane_host(w, W, L), m)
+        # bit b of word (s, x) is cell (x, 32 s + b)
+        x, y = W - 1, L - 1
+        assert bool((w[(y >> 5) * Wp + x] >> (y & 31)) & 1) == bool(m[x, y])
+
+
+def test_builtin_and_committed_grid_sets():
+    train, test = maps.gridload(None)
+    assert len(train) == 6 and len(test) == 3 and all(g.shape == (15, 15) for g in train + test)
+    g100 = maps.load_grid_set("bg2_100x100")
+    assert len(g100) == 75 and g100[0].shape == (100, 100)
+    assert set(np.unique(g100[0])) <= {-1.0, 1.0}
+    tr, te = maps.gridload({"grid_dir": "./Grids/bg2_100x100", "numgrids": 20})
+    assert len(tr) == 10 and len(te) == 10             # gridmaker.py:96-102 half split
+    with pytest.raises(ValueError):
+        maps.grids_to_cells([np.full((4, 4), 0.5)])
+
+
+def test_gridgen_matches_reference_contract():
+    np.random.seed(3)
+    tr, te = maps.gridgen({"prob_obst": 0.2, "gridwidth": 12, "gridlen": 9, "numgrids": 4})
+    assert len(tr) == 4 and all(g.shape == (12, 9) for g in tr)
+    assert set(np.unique(np.stack(tr))) <= {-1.0, 1.0}
+
+
+def test_action_forms():
+    import torch
+    assert _scalar_action(None) == ("sentinel", -1)
+    assert _scalar_action(-1) == ("sentinel", -1)
+    assert _scalar_action(np.int64(27)) == ("joint", 27)
+    assert _scalar_action(torch.tensor(5)) == ("joint", 5)
+    kind, v = _scalar_action([0, 3, 2])
+    assert kind == "per_robot" and v.tolist() == [0, 3, 2]
+    np.random.seed(0)
+    d = Discrete(256)
+    s = d.sample()
+    assert 0 <= int(s) < 256 and d.sample(5).shape == (5,)
+    assert oc.decode_base4(27, 4).tolist() == [3, 2, 1, 0]
+
+
+def test_lidar_beam_table_is_the_oracles():
+    for n in (1, 5, 21, 31):
+        assert np.array_equal(lidar_beam_table(n), oc.lidar_beam_table(n))
+    with pytest.raises(AssertionError):
+        LidarSensor({"num_lasers": 20, "range": 4})
+    assert SquareSensor({"range": 2}).env_keys()["sensor_config"] == {"range": 2}
+
+
+def test_algorithmic_bytes_match_survey():
+    import bench
+    kind, grid, E, cfg, _ = bench.WORKLOADS["c2"]
+    assert bench.alg_bytes_per_env_step(kind, cfg, 102, 102) == 7769
+    kind, grid, E, cfg, _ = bench.WORKLOADS["c3"]
+    assert bench.alg_bytes_per_env_step(kind, cfg, 258, 258) == 23341
