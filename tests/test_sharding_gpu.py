@@ -42,4 +42,6 @@ def test_logical_shards_equal_single_batch(shards):
             assert torch.equal(p.reward64, whole.reward64[lo:hi])
             tot_parts += p.stats.cpu().numpy()
     assert tot_whole[0] > 0                               # episodes did finish and auto-reset
-    assert np.array_equal(tot_whole, tot_parts)
+    idx = [0, 1, 2, 4, 5, 6]                              # integer-valued sums: exact in any order
+    assert np.array_equal(tot_whole[idx], tot_parts[idx])
+    assert np.allclose(tot_whole[3], tot_parts[3], rtol=1e-12)   # coverage fractions: order of summation differs
