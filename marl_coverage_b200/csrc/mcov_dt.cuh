@@ -22,22 +22,36 @@ __host__ __device__ inline int dt_pitch_of(const Geometry& g) {
     return 2 * words;
 }
 
+// Shared scratch the transform needs besides the distance buffer: 2 ints + 2 * max(blockDim, L) ints.
+__host__ __device__ inline int dt_scratch_ints(int L, int threads) { return 2 + 2 * (L > threads ? L : threads); }
+
 // d[x * pitch + y] = taxicab distance from (x, y) to the nearest ZERO pixel (0 on zero pixels).
 // `zero_word(strip, x)` returns the zero-pixel bits of one plane word (bit b <-> y = 32*strip + b);
-// bits with y >= L must be 0.  Pass 1 runs along y in closed form on the bit words; pass 2 is the
-// min-plus sweep along x.  All threads of the CTA must call; `red` is 2 ints of shared scratch.
+// bits with y >= L must be 0.
+//   pass 1 (along y): closed form on the bit words with clz / ffs — no sequential scan;
+//   pass 2 (along x): min-plus sweep, each column cut into `nch` chunks so that L * nch threads work:
+//     local forward+backward scan per chunk, chunk-end values combined across chunks (min-plus is
+//     associative: entering a chunk with carry c adds c + offset), then applied in a second sweep.
+// All threads of the CTA must call; `red` is dt_scratch_ints(L, blockDim.x) ints of shared scratch.
 template <class ZeroWord>
 __device__ DtResult l1_transform(ZeroWord zero_word, const Geometry& g, uint16_t* d, int pitch, int* red) {
     constexpr unsigned FULLM = 0xffffffffu;
     const int W = g.W, L = g.L, strips = g.strips;
+    const int T = blockDim.x;
     if (threadIdx.x == 0) { red[0] = 0; red[1] = 0; }
     __syncthreads();
     int anyz = 0;
     const int nw = W * strips;
-    for (int idx = threadIdx.x; idx < nw; idx += blockDim.x) {
+    for (int idx = threadIdx.x; idx < nw; idx += T) {
         const int s = idx / W, x = idx - s * W;              // x fastest within a strip
         const uint32_t z = zero_word(s, x);
         anyz |= (z != 0u);
+        uint32_t* drow = reinterpret_cast<uint32_t*>(d + (size_t)x * pitch + 32 * s);
+        if (z == FULLM) {                                    // common early in an episode: all zero pixels
+#pragma unroll
+            for (int j = 0; j < 16; ++j) drow[j] = 0u;
+            continue;
+        }
         int base_lo = DT_INF, base_hi = DT_INF;              // gap to the nearest zero pixel in other strips
         for (int ss = s - 1; ss >= 0; --ss) {
             const uint32_t t = zero_word(ss, x);
@@ -47,7 +61,6 @@ __device__ DtResult l1_transform(ZeroWord zero_word, const Geometry& g, uint16_t
             const uint32_t t = zero_word(ss, x);
             if (t) { base_hi = 32 * (ss - s) + (__ffs(t) - 1) - 31; break; }
         }
-        uint32_t* drow = reinterpret_cast<uint32_t*>(d + (size_t)x * pitch + 32 * s);
 #pragma unroll 4
         for (int j = 0; j < 16; ++j) {
             uint32_t packed = 0;
@@ -64,33 +77,67 @@ __device__ DtResult l1_transform(ZeroWord zero_word, const Geometry& g, uint16_t
         }
     }
     anyz = __syncthreads_or(anyz);
-    int mx = 0;
-    for (int y = threadIdx.x; y < L; y += blockDim.x) {
+
+    // ---- pass 2 ----------------------------------------------------------------------------------
+    int nch = T / L;
+    if (nch < 1) nch = 1;
+    if (nch > W) nch = W;
+    const int K = (W + nch - 1) / nch;                       // rows per chunk
+    int* endF = red + 2;                                     // [nch][L] forward value at the chunk's last row
+    int* endB = endF + (L > T ? L : T);                      // [nch][L] backward value at the chunk's first row
+    const int items = L * nch;
+    for (int it = threadIdx.x; it < items; it += T) {
+        const int c = it / L, y = it - c * L;
+        const int x0 = c * K, x1 = min(x0 + K, W);
         uint16_t* col = d + y;
         int v = DT_INF;
-        for (int x0 = 0; x0 < W; x0 += 8) {
+        for (int xb = x0; xb < x1; xb += 8) {
             int t[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = (x0 + k < W) ? (int)col[(size_t)(x0 + k) * pitch] : DT_INF;
+            for (int k = 0; k < 8; ++k) t[k] = (xb + k < x1) ? (int)col[(size_t)(xb + k) * pitch] : DT_INF;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                v = min(min(t[k], v + 1), DT_INF);
-                if (x0 + k < W) col[(size_t)(x0 + k) * pitch] = (uint16_t)v;
-            }
-        }
-        v = DT_INF;
-        for (int x0 = W - 1; x0 >= 0; x0 -= 8) {
-            int t[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = (x0 - k >= 0) ? (int)col[(size_t)(x0 - k) * pitch] : DT_INF;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                if (x0 - k >= 0) {
+            for (int k = 0; k < 8; ++k)
+                if (xb + k < x1) {
                     v = min(min(t[k], v + 1), DT_INF);
-                    col[(size_t)(x0 - k) * pitch] = (uint16_t)v;
-                    mx = max(mx, v);
+                    col[(size_t)(xb + k) * pitch] = (uint16_t)v;
                 }
-            }
+        }
+        endF[it] = x1 > x0 ? v : DT_INF;
+        v = DT_INF;
+        for (int xb = x1 - 1; xb >= x0; xb -= 8) {
+            int t[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = (xb - k >= x0) ? (int)col[(size_t)(xb - k) * pitch] : DT_INF;
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (xb - k >= x0) {
+                    v = min(min(t[k], v + 1), DT_INF);
+                    col[(size_t)(xb - k) * pitch] = (uint16_t)v;
+                }
+        }
+        endB[it] = x1 > x0 ? v : DT_INF;
+    }
+    __syncthreads();
+    int mx = 0;
+    for (int it = threadIdx.x; it < items; it += T) {
+        const int c = it / L, y = it - c * L;
+        const int x0 = c * K, x1 = min(x0 + K, W);
+        // carry entering from the left = global forward value at row x0 - 1; from the right likewise
+        int cf = DT_INF, cb = DT_INF;
+        for (int cc = 0; cc < c; ++cc) cf = min(endF[cc * L + y], cf + (min(cc * K + K, W) - cc * K));
+        for (int cc = nch - 1; cc > c; --cc) {
+            const int a0 = cc * K, a1 = min(a0 + K, W);
+            if (a1 > a0) cb = min(endB[cc * L + y], cb + (a1 - a0));
+        }
+        cf = min(cf, DT_INF);
+        cb = min(cb, DT_INF);
+        uint16_t* col = d + y;
+        for (int x = x0; x < x1; ++x) {
+            int v = (int)col[(size_t)x * pitch];
+            v = min(v, min(cf + (x - x0 + 1), cb + (x1 - x)));
+            v = min(v, DT_INF);
+            col[(size_t)x * pitch] = (uint16_t)v;
+            mx = max(mx, v);
         }
     }
     mx = __reduce_max_sync(FULLM, mx);

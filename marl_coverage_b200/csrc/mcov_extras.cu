@@ -36,7 +36,7 @@ struct ExtrasParams {
 };
 
 struct ExtrasSmem {
-    int red[2];
+    int red0;
     uint32_t goal;
     int flag;
 };
@@ -54,7 +54,10 @@ dec_extras_kernel(const ExtrasParams p) {
     const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
     const int N = p.N, ego = p.ego, ow = p.ow, pad = p.pad, pitch = p.pitch;
     const int lastbits = L & 31;
-    unsigned char* work = p.scratch ? p.scratch + (size_t)blockIdx.x * p.work_bytes : smem_raw;
+    // dynamic shared memory: [transform scratch ints][work area unless it lives in global scratch]
+    int* red = reinterpret_cast<int*>(smem_raw);
+    const int head_bytes = (dt_scratch_ints(L, XT) * 4 + 15) & ~15;
+    unsigned char* work = p.scratch ? p.scratch + (size_t)blockIdx.x * p.work_bytes : smem_raw + head_bytes;
     uint16_t* dbuf = reinterpret_cast<uint16_t*>(work);                       // [W][pitch]
     uint32_t* planes = reinterpret_cast<uint32_t*>(work + (((size_t)W * pitch * 2 + 15) & ~(size_t)15));
     uint32_t* visited = planes;
@@ -79,7 +82,7 @@ dec_extras_kernel(const ExtrasParams p) {
                     [&](int ss, int x) -> uint32_t {
                         const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
                         return plane[ss * Wp + x].x & valid;
-                    }, p.g, dbuf, pitch, sm.red);
+                    }, p.g, dbuf, pitch, red);
                 // max over the PADDED image: edge cells push their distance outwards by `pad`
                 int mx = r.dmax;
                 if (r.any_zero && pad > 0) {
@@ -92,11 +95,11 @@ dec_extras_kernel(const ExtrasParams p) {
                         m2 = max(m2, (int)dbuf[(size_t)x * pitch + y] + ex + ey);
                     }
                     m2 = __reduce_max_sync(FULL, m2);
-                    if (threadIdx.x == 0) sm.red[0] = 0;
+                    if (threadIdx.x == 0) sm.red0 = 0;
                     __syncthreads();
-                    if ((threadIdx.x & 31) == 0) atomicMax(&sm.red[0], m2);
+                    if ((threadIdx.x & 31) == 0) atomicMax(&sm.red0, m2);
                     __syncthreads();
-                    mx = max(mx, sm.red[0]);
+                    mx = max(mx, sm.red0);
                 }
                 if (p.pre_sense) {
                     // quirk A.3.11: the padded map is indexed with UNpadded coordinates; float32 sum
@@ -247,8 +250,9 @@ inline ExtrasShape extras_shape(const mcov_env* env) {
     const size_t lev = ((size_t)env->g.W * s.pitch * 2 + 15) & ~(size_t)15;
     s.work_bytes = lev + (size_t)3 * env->g.PW * 4;
     s.work_bytes = (s.work_bytes + 255) & ~(size_t)255;
-    s.global_work = s.work_bytes > 200 * 1024;
-    s.smem = s.global_work ? 0 : s.work_bytes;
+    const size_t head = ((size_t)dt_scratch_ints(env->g.L, XT) * 4 + 15) & ~(size_t)15;
+    s.global_work = s.work_bytes + head > 200 * 1024;
+    s.smem = head + (s.global_work ? 0 : s.work_bytes);
     int per_sm = s.global_work ? 2 : (int)((220 * 1024) / (s.smem + 2048));
     if (per_sm > 8) per_sm = 8;
     if (per_sm < 1) per_sm = 1;

@@ -37,19 +37,30 @@ struct SuperSmem {
     uint2 rows[MCOV_MAX_ROBOTS * MAXS];       // per (robot, footprint row): .x new cells worth 1, .y re-covered
     uint32_t pos[MCOV_MAX_ROBOTS];            // poses after the moves
     int any_zero, dmax, covered, again, skip, last;
-    int red[2];
+};
+
+// dynamic shared memory: [dt scratch ints][distance LUT floats: W + L + 2][distance work buffer]
+struct SuperDyn {
+    int* red;
+    float* dlut;
+    uint16_t* dbuf;
 };
 
 // Distance transform of the covered plane: zero pixels are the NOT-covered in-map cells
 // (obstacles included) — super_grid_rl.py:292-295.
-__device__ void super_transform(const uint32_t* cov, const Geometry& g, uint16_t* d, int pitch, SuperSmem& sm) {
+// Also fills the value table dlut[d] = 1 - d / max(d) (float32, super_grid_rl.py:297-303) so that the
+// state writer and the reward lookup never divide.
+__device__ void super_transform(const uint32_t* cov, const Geometry& g, const SuperDyn& dyn, int pitch,
+                                SuperSmem& sm) {
     const int Wp = g.Wp, strips = g.strips, lastbits = g.L & 31;
     const DtResult r = l1_transform(
         [&](int ss, int x) -> uint32_t {
             const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
             return ~cov[ss * Wp + x] & valid;
-        }, g, d, pitch, sm.red);
+        }, g, dyn.dbuf, pitch, dyn.red);
     if (threadIdx.x == 0) { sm.any_zero = r.any_zero; sm.dmax = r.dmax; }
+    if (r.any_zero)
+        for (int k = threadIdx.x; k <= r.dmax; k += blockDim.x) dyn.dlut[k] = dist_value(k, 1, r.dmax);
     __syncthreads();
 }
 
@@ -75,20 +86,30 @@ __device__ double numpy_sum(const double* a, int n) {
 // ---- state tensor (super_grid_rl.py:305-341) ------------------------------------------------------
 // [pos_0 .. pos_{N-1} | one merged plane with use_scanning] [observed obstacles] [free = NOT covered]
 // [distance channel], each W x L float32, y fastest.
-__device__ void write_state(const SuperParams& p, SuperSmem& sm, const uint16_t* dbuf, int e,
+// Zero fill of the position planes (vectorised path): independent of the dynamics, so warps 1..15 run
+// it while warp 0 resolves the moves; the N occupied cells are patched by write_state afterwards.
+__device__ __forceinline__ void fill_position_planes(const SuperParams& p, int e, int first, int nthreads) {
+    const int qp = (p.g.W * p.g.L) >> 2;
+    const int nz = (p.use_scanning ? 1 : p.N) * qp;
+    float4* dst = reinterpret_cast<float4*>(p.obs + (size_t)e * p.C * p.g.W * p.g.L);
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = (int)threadIdx.x - first; q < nz; q += nthreads) __stcs(dst + q, z4);
+}
+
+__device__ void write_state(const SuperParams& p, SuperSmem& sm, const SuperDyn& dy, int e,
                             const uint32_t* cov, const uint32_t* seen) {
+    const uint16_t* dbuf = dy.dbuf;
+    const float* dlut = dy.dlut;
     const int N = p.N, W = p.g.W, L = p.g.L, Wp = p.g.Wp;
     const int WL = W * L, pitch = p.dt_pitch;
     const int npos = p.use_scanning ? 1 : N;
-    const int any_zero = sm.any_zero, dmax = sm.dmax;
-    const bool flat_one = sm.covered == 0;                   // nothing covered: channel is all 1
+    // nothing covered (or no division, :299): channel is all 1; no zero pixel at all: all 0 (cv2 FLT_MAX)
+    const bool flat = sm.covered == 0 || !sm.any_zero || sm.dmax <= 0;
+    const float flat_v = (sm.covered == 0 || sm.any_zero) ? 1.0f : 0.0f;
     float* obs_e = p.obs + (size_t)e * p.C * WL;
     if (p.vec_ok) {
         const int Lq = L >> 2, qp = WL >> 2;
         float4* dst = reinterpret_cast<float4*>(obs_e);
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int nz = npos * qp;
-        for (int q = threadIdx.x; q < nz; q += ST) __stcs(dst + q, z4);
         float4* d_obst = dst + (size_t)npos * qp;
         float4* d_free = d_obst + qp;
         float4* d_dist = d_free + qp;
@@ -100,15 +121,15 @@ __device__ void write_state(const SuperParams& p, SuperSmem& sm, const uint16_t*
             __stcs(d_obst + q, sm.lut[(so >> nib) & 15u]);
             __stcs(d_free + q, sm.lut[(~cv >> nib) & 15u]);
             float4 dv;
-            if (flat_one) {
-                dv = make_float4(1.f, 1.f, 1.f, 1.f);
+            if (flat) {
+                dv = make_float4(flat_v, flat_v, flat_v, flat_v);
             } else {
                 const uint32_t* dp = reinterpret_cast<const uint32_t*>(dbuf + (size_t)x * pitch + 4 * yq);
                 const uint32_t a = dp[0], b = dp[1];
-                dv.x = dist_value((int)(a & 0xffffu), any_zero, dmax);
-                dv.y = dist_value((int)(a >> 16), any_zero, dmax);
-                dv.z = dist_value((int)(b & 0xffffu), any_zero, dmax);
-                dv.w = dist_value((int)(b >> 16), any_zero, dmax);
+                dv.x = dlut[a & 0xffffu];
+                dv.y = dlut[a >> 16];
+                dv.z = dlut[b & 0xffffu];
+                dv.w = dlut[b >> 16];
             }
             __stcs(d_dist + q, dv);
             x += dx;
@@ -139,7 +160,7 @@ __device__ void write_state(const SuperParams& p, SuperSmem& sm, const uint16_t*
                 const int w = (y >> 5) * Wp + x, b = y & 31;
                 if (c == npos) v = (float)((seen[w] >> b) & 1u);
                 else if (c == npos + 1) v = (float)((~cov[w] >> b) & 1u);
-                else v = flat_one ? 1.0f : dist_value((int)dbuf[(size_t)x * pitch + y], any_zero, dmax);
+                else v = flat ? flat_v : dlut[dbuf[(size_t)x * pitch + y]];
             }
             __stcs(obs_e + k, v);
         }
@@ -148,7 +169,8 @@ __device__ void write_state(const SuperParams& p, SuperSmem& sm, const uint16_t*
 
 // One pass over env e in `mode`.  Returns true when the env finished and must be re-seeded in place
 // by a second (MODE_RESET) pass of the same CTA (fused auto-reset).
-__device__ bool super_pass(const SuperParams& p, SuperSmem& sm, uint16_t* dbuf, const int e, const int mode) {
+__device__ bool super_pass(const SuperParams& p, SuperSmem& sm, const SuperDyn& dy, const int e, const int mode) {
+    uint16_t* const dbuf = dy.dbuf;
     const int N = p.N, R = p.R, S = 2 * R + 1;
     const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -187,7 +209,11 @@ __device__ bool super_pass(const SuperParams& p, SuperSmem& sm, uint16_t* dbuf, 
     if (mode == MODE_STEP && p.act_fmt == MCOV_ACT_I64_BASE4)
         sentinel = (reinterpret_cast<const long long*>(p.actions)[e] == -1);
     const bool dyn = (mode == MODE_STEP) && !sentinel;
-    if (dyn && p.dist_reward) super_transform(cov, p.g, dbuf, p.dt_pitch, sm);   // start-of-step map (:117-118)
+    if (dyn && p.dist_reward) super_transform(cov, p.g, dy, p.dt_pitch, sm);     // start-of-step map (:117-118)
+    if (p.vec_ok) {
+        if (fresh) fill_position_planes(p, e, 0, ST);
+        else if (warp != 0) fill_position_planes(p, e, 32, ST - 32);
+    }
 
     if (warp == 0 && !fresh) {
         const int map_idx = head->map_idx;
@@ -355,22 +381,27 @@ __device__ bool super_pass(const SuperParams& p, SuperSmem& sm, uint16_t* dbuf, 
     if (sm.again) return true;                                // state comes from the reset pass
 
     if (sm.covered > 0) {
-        super_transform(cov, p.g, dbuf, p.dt_pitch, sm);
+        super_transform(cov, p.g, dy, p.dt_pitch, sm);
     } else if (threadIdx.x == 0) {
         sm.any_zero = 1;
         sm.dmax = 0;
     }
     __syncthreads();
-    write_state(p, sm, dbuf, e, cov, seen);
+    write_state(p, sm, dy, e, cov, seen);
     return false;
 }
 
-__global__ void __launch_bounds__(ST)
+__global__ void __launch_bounds__(ST, 3)
 super_env_kernel(const SuperParams p, const int dt_cells) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SuperSmem sm;
-    uint16_t* dbuf = p.dt_scratch ? p.dt_scratch + (size_t)blockIdx.x * dt_cells
-                                  : reinterpret_cast<uint16_t*>(smem_raw);
+    SuperDyn dy;
+    dy.red = reinterpret_cast<int*>(smem_raw);
+    const int nred = dt_scratch_ints(p.g.L, ST);
+    dy.dlut = reinterpret_cast<float*>(dy.red + nred);
+    const int head_bytes = ((nred + p.g.W + p.g.L + 2) * 4 + 15) & ~15;
+    dy.dbuf = p.dt_scratch ? p.dt_scratch + (size_t)blockIdx.x * dt_cells
+                           : reinterpret_cast<uint16_t*>(smem_raw + head_bytes);
     if (threadIdx.x < 16) {
         const uint32_t t = threadIdx.x;
         sm.lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
@@ -387,7 +418,7 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
             else if (p.mask_from_flags) act = p.needs_reset[e];
             if (!act) continue;                               // CTA-uniform
         }
-        while (super_pass(p, sm, dbuf, e, m)) m = MODE_RESET; // fused auto-reset
+        while (super_pass(p, sm, dy, e, m)) m = MODE_RESET; // fused auto-reset
     }
 
     // ---- episode statistics: CTA row -> last CTA folds all rows (single launch) -------------------
@@ -423,9 +454,10 @@ inline SuperShape super_shape(const mcov_env* env) {
     s.pitch = dt_pitch_of(env->g);
     s.cells = env->g.W * s.pitch;
     const size_t bytes = (size_t)s.cells * 2;
-    s.global_dt = bytes > 200 * 1024;
-    s.smem = s.global_dt ? 0 : ((bytes + 15) / 16 * 16);
-    int per_sm = 4;
+    const size_t head = (((size_t)dt_scratch_ints(env->g.L, ST) + env->g.W + env->g.L + 2) * 4 + 15) & ~(size_t)15;
+    s.global_dt = bytes + head > 200 * 1024;
+    s.smem = head + (s.global_dt ? 0 : ((bytes + 15) / 16 * 16));
+    int per_sm = 3;                                          // __launch_bounds__(ST, 3)
     if (!s.global_dt) {
         const int by_smem = (int)((220 * 1024) / (s.smem + sizeof(SuperSmem) + 1024));
         if (per_sm > by_smem) per_sm = by_smem;
@@ -453,10 +485,16 @@ cudaError_t launch_super(mcov_env* env, SuperParams& p, cudaStream_t st) {
     p.dt_pitch = s.pitch;
     if (s.global_dt && !p.dt_scratch) return cudaErrorInvalidValue;
     if (!s.global_dt) p.dt_scratch = nullptr;
-    if (s.smem > 40 * 1024) {
-        cudaError_t err = cudaFuncSetAttribute(super_env_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               (int)s.smem);
+    static size_t configured_smem = 0;                        // one process drives one device
+    if (s.smem > configured_smem) {
+        cudaError_t err = cudaSuccess;
+        if (s.smem > 38 * 1024)
+            err = cudaFuncSetAttribute(super_env_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
+        if (err == cudaSuccess)
+            err = cudaFuncSetAttribute(super_env_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       (int)cudaSharedmemCarveoutMaxShared);
         if (err != cudaSuccess) return err;
+        configured_smem = s.smem;
     }
     super_env_kernel<<<s.grid, ST, s.smem, st>>>(p, s.cells);
     env->launches++;
