@@ -83,39 +83,50 @@ __device__ double numpy_sum(const double* a, int n) {
     return res;
 }
 
+// Per-env hand-over from the dynamics warp to the state writers (double buffered).
+struct EnvSlot {
+    uint32_t pos[MCOV_MAX_ROBOTS];            // poses after the moves
+    int covered;                              // covered-cell count after the step (0: nothing to transform)
+};
+
 // ---- state tensor (super_grid_rl.py:305-341) ------------------------------------------------------
 // [pos_0 .. pos_{N-1} | one merged plane with use_scanning] [observed obstacles] [free = NOT covered]
-// [distance channel], each W x L float32, y fastest.
-// Zero fill of the position planes (vectorised path): independent of the dynamics, so warps 1..15 run
-// it while warp 0 resolves the moves; the N occupied cells are patched by write_state afterwards.
-__device__ __forceinline__ void fill_position_planes(const SuperParams& p, int e, int first, int nthreads) {
-    const int qp = (p.g.W * p.g.L) >> 2;
-    const int nz = (p.use_scanning ? 1 : p.N) * qp;
-    float4* dst = reinterpret_cast<float4*>(p.obs + (size_t)e * p.C * p.g.W * p.g.L);
-    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int q = (int)threadIdx.x - first; q < nz; q += nthreads) __stcs(dst + q, z4);
-}
-
-__device__ void write_state(const SuperParams& p, SuperSmem& sm, const SuperDyn& dy, int e,
-                            const uint32_t* cov, const uint32_t* seen) {
+// [distance channel], each W x L float32, y fastest.  Written by threads [first, first + nthreads)
+// of the CTA; no barrier inside: the thread that zero-fills the float4 holding a robot's cell also
+// patches the 1.0 into it (same thread, same address: program order).
+__device__ void write_state(const SuperParams& p, const SuperSmem& sm, const EnvSlot& slot, const SuperDyn& dy,
+                            int e, int first, int nthreads) {
+    const int rank = (int)threadIdx.x - first;
+    if (rank < 0 || rank >= nthreads) return;
     const uint16_t* dbuf = dy.dbuf;
     const float* dlut = dy.dlut;
     const int N = p.N, W = p.g.W, L = p.g.L, Wp = p.g.Wp;
     const int WL = W * L, pitch = p.dt_pitch;
     const int npos = p.use_scanning ? 1 : N;
+    const uint32_t* cov = p.covered + (size_t)e * p.g.PW;
+    const uint32_t* seen = p.seen_obst + (size_t)e * p.g.PW;
     // nothing covered (or no division, :299): channel is all 1; no zero pixel at all: all 0 (cv2 FLT_MAX)
-    const bool flat = sm.covered == 0 || !sm.any_zero || sm.dmax <= 0;
-    const float flat_v = (sm.covered == 0 || sm.any_zero) ? 1.0f : 0.0f;
+    const bool flat = slot.covered == 0 || !sm.any_zero || sm.dmax <= 0;
+    const float flat_v = (slot.covered == 0 || sm.any_zero) ? 1.0f : 0.0f;
     float* obs_e = p.obs + (size_t)e * p.C * WL;
     if (p.vec_ok) {
         const int Lq = L >> 2, qp = WL >> 2;
         float4* dst = reinterpret_cast<float4*>(obs_e);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int nz = npos * qp;
+        for (int q = rank; q < nz; q += nthreads) __stcs(dst + q, z4);
+        for (int j = 0; j < N; ++j) {
+            const uint32_t pv = slot.pos[j];
+            const int cell = unpack_x(pv) * L + unpack_y(pv);
+            const int q = (p.use_scanning ? 0 : j) * qp + (cell >> 2);
+            if (q % nthreads == rank) obs_e[(size_t)(p.use_scanning ? 0 : j) * WL + cell] = 1.0f;
+        }
         float4* d_obst = dst + (size_t)npos * qp;
         float4* d_free = d_obst + qp;
         float4* d_dist = d_free + qp;
-        int x = threadIdx.x / Lq, yq = threadIdx.x - x * Lq;
-        const int dx = ST / Lq, dyq = ST - dx * Lq;
-        for (int q = threadIdx.x; q < qp; q += ST) {
+        int x = rank / Lq, yq = rank - x * Lq;
+        const int dx = nthreads / Lq, dyq = nthreads - dx * Lq;
+        for (int q = rank; q < qp; q += nthreads) {
             const int w = (yq >> 3) * Wp + x, nib = (yq & 7) * 4;
             const uint32_t so = seen[w], cv = cov[w];
             __stcs(d_obst + q, sm.lut[(so >> nib) & 15u]);
@@ -136,25 +147,19 @@ __device__ void write_state(const SuperParams& p, SuperSmem& sm, const SuperDyn&
             yq += dyq;
             if (yq >= Lq) { yq -= Lq; ++x; }
         }
-        __syncthreads();                                     // zero fill is ordered before the 1.0 patches
-        if (threadIdx.x < N) {
-            const uint32_t pv = sm.pos[threadIdx.x];
-            const int plane = p.use_scanning ? 0 : threadIdx.x;
-            obs_e[(size_t)plane * WL + unpack_x(pv) * L + unpack_y(pv)] = 1.0f;
-        }
     } else {
         // generic path (L not a multiple of 4 or unaligned buffer): one float per thread
         const int total = p.C * WL;
-        for (int k = threadIdx.x; k < total; k += ST) {
+        for (int k = rank; k < total; k += nthreads) {
             const int c = k / WL, rem = k - c * WL;
             const int x = rem / L, y = rem - x * L;
             float v;
             if (c < npos) {
                 v = 0.0f;
                 if (p.use_scanning) {
-                    for (int j = 0; j < N; ++j) v = (sm.pos[j] == pack_xy(x, y)) ? 1.0f : v;
+                    for (int j = 0; j < N; ++j) v = (slot.pos[j] == pack_xy(x, y)) ? 1.0f : v;
                 } else {
-                    v = (sm.pos[c] == pack_xy(x, y)) ? 1.0f : 0.0f;
+                    v = (slot.pos[c] == pack_xy(x, y)) ? 1.0f : 0.0f;
                 }
             } else {
                 const int w = (y >> 5) * Wp + x, b = y & 31;
@@ -167,234 +172,231 @@ __device__ void write_state(const SuperParams& p, SuperSmem& sm, const SuperDyn&
     }
 }
 
-// One pass over env e in `mode`.  Returns true when the env finished and must be re-seeded in place
-// by a second (MODE_RESET) pass of the same CTA (fused auto-reset).
-__device__ bool super_pass(const SuperParams& p, SuperSmem& sm, const SuperDyn& dy, const int e, const int mode) {
+// Episode start for env e, by warp 0 alone (super_grid_rl.py:343-399): new map, new poses, nothing
+// covered, nothing sensed.  Does not touch a_prev / done_thresh (they persist).
+__device__ void super_reset_env(const SuperParams& p, EnvSlot& slot, int e, int lane) {
+    const int N = p.N, PW = p.g.PW;
+    unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
+    EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
+    uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
+    int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
+    if (lane == 0) {
+        int mi = 0;
+        draw_starts(p.wall, p.g, N, p.n_maps, p.map_idx_in, p.start_xy_in, p.seed,
+                    (uint32_t)(p.env_id_base + e), e, head->episode, slot.pos, &mi);
+        head->currstep = 0;
+        head->map_idx = mi;
+        head->episode = head->episode + 1;
+        head->ep_return = 0.0;
+        hcov[0] = 0;
+        for (int j = 0; j < N; ++j) hpos[j] = slot.pos[j];
+        p.needs_reset[e] = 0;
+        slot.covered = 0;
+    }
+    uint4* zc = reinterpret_cast<uint4*>(p.covered + (size_t)e * PW);
+    uint4* zs = reinterpret_cast<uint4*>(p.seen_obst + (size_t)e * PW);
+    for (int k = lane; k < PW / 4; k += 32) {
+        zc[k] = make_uint4(0, 0, 0, 0);
+        zs[k] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
+}
+
+// Dynamics of env e by warp 0 alone: action decode, scan order, collision-checked moves, footprints,
+// reward, termination, statistics and — when the episode ended and auto_reset is on — the re-seed of
+// the env in place.  Leaves poses + covered count in `slot` for the state writers.
+__device__ void super_dynamics(const SuperParams& p, SuperSmem& sm, EnvSlot& slot, const SuperDyn& dy,
+                               const int e, const int mode, const int lane) {
     uint16_t* const dbuf = dy.dbuf;
     const int N = p.N, R = p.R, S = 2 * R + 1;
     const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char* hrec = p.hdr + (size_t)e * p.hdr_stride;
     EnvHead* head = reinterpret_cast<EnvHead*>(hrec);
     uint32_t* hpos = reinterpret_cast<uint32_t*>(hrec + p.off_pos);
     int32_t* hcov = reinterpret_cast<int32_t*>(hrec + p.off_cov);
     uint32_t* cov = p.covered + (size_t)e * PW;
     uint32_t* seen = p.seen_obst + (size_t)e * PW;
-    const bool fresh = (mode == MODE_RESET);
-
-    __syncthreads();                                         // previous pass is done with shared memory
-    if (fresh) {
-        // super_grid_rl.py:343-399: new map, new poses, nothing covered, nothing sensed
-        if (threadIdx.x == 0) {
-            int mi = 0;
-            draw_starts(p.wall, p.g, N, p.n_maps, p.map_idx_in, p.start_xy_in, p.seed,
-                        (uint32_t)(p.env_id_base + e), e, head->episode, sm.pos, &mi);
-            head->currstep = 0;
-            head->map_idx = mi;
-            head->episode = head->episode + 1;
-            head->ep_return = 0.0;
-            hcov[0] = 0;
-            for (int j = 0; j < N; ++j) hpos[j] = sm.pos[j];
-            p.needs_reset[e] = 0;
-            sm.covered = 0;
-        }
-        uint4* zc = reinterpret_cast<uint4*>(cov);
-        uint4* zs = reinterpret_cast<uint4*>(seen);
-        for (int k = threadIdx.x; k < PW / 4; k += ST) {
-            zc[k] = make_uint4(0, 0, 0, 0);
-            zs[k] = make_uint4(0, 0, 0, 0);
-        }
+    if (mode == MODE_RESET) {
+        super_reset_env(p, slot, e, lane);
+        return;
     }
     bool sentinel = false;
     if (mode == MODE_STEP && p.act_fmt == MCOV_ACT_I64_BASE4)
         sentinel = (reinterpret_cast<const long long*>(p.actions)[e] == -1);
     const bool dyn = (mode == MODE_STEP) && !sentinel;
-    if (dyn && p.dist_reward) super_transform(cov, p.g, dy, p.dt_pitch, sm);     // start-of-step map (:117-118)
-    if (p.vec_ok) {
-        if (fresh) fill_position_planes(p, e, 0, ST);
-        else if (warp != 0) fill_position_planes(p, e, 32, ST - 32);
-    }
-
-    if (warp == 0 && !fresh) {
-        const int map_idx = head->map_idx;
-        const uint32_t* wall = p.wall + (size_t)map_idx * PW;
-        const uint32_t* tpos = p.pos + (size_t)map_idx * PW;
-        const uint32_t myv = lane < N ? hpos[lane] : 0xffffffffu;
-        uint32_t pv = myv;
-        if (dyn) {
-            // ---- action decode (:92-100): digit c of the joint action drives control slot c ----
-            int u = 0;
-            if (p.act_fmt == MCOV_ACT_I64_BASE4)
-                u = (int)((reinterpret_cast<const long long*>(p.actions)[e] >> (2 * lane)) & 3);
-            else if (lane < N)
-                u = (int)(reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * N + lane] & 3u);
-            // ---- scan order (:107-111,125-129): control c goes to the c-th robot in raster order of
-            // the start-of-step poses (key x + y*W, ties by index)
-            int rank = lane, zc = lane;
-            if (p.use_scanning) {
-                const int key = unpack_x(myv) + unpack_y(myv) * W;
-                rank = 0;
-                for (int j = 0; j < N; ++j) {
-                    const int kj = __shfl_sync(FULL, key, j);
-                    rank += (kj < key) || (kj == key && j < lane);
-                }
-                for (int j = 0; j < N; ++j)
-                    if (__shfl_sync(FULL, rank, j) == lane) zc = j;
+    int again = 0;
+    {
+    const int map_idx = head->map_idx;
+    const uint32_t* wall = p.wall + (size_t)map_idx * PW;
+    const uint32_t* tpos = p.pos + (size_t)map_idx * PW;
+    const uint32_t myv = lane < N ? hpos[lane] : 0xffffffffu;
+    uint32_t pv = myv;
+    if (dyn) {
+        // ---- action decode (:92-100): digit c of the joint action drives control slot c ----
+        int u = 0;
+        if (p.act_fmt == MCOV_ACT_I64_BASE4)
+            u = (int)((reinterpret_cast<const long long*>(p.actions)[e] >> (2 * lane)) & 3);
+        else if (lane < N)
+            u = (int)(reinterpret_cast<const uint8_t*>(p.actions)[(size_t)e * N + lane] & 3u);
+        // ---- scan order (:107-111,125-129): control c goes to the c-th robot in raster order of
+        // the start-of-step poses (key x + y*W, ties by index)
+        int rank = lane, zc = lane;
+        if (p.use_scanning) {
+            const int key = unpack_x(myv) + unpack_y(myv) * W;
+            rank = 0;
+            for (int j = 0; j < N; ++j) {
+                const int kj = __shfl_sync(FULL, key, j);
+                rank += (kj < key) || (kj == key && j < lane);
             }
-            // ---- sequential, collision-checked moves (:121-174).  Super table: 0:x-1 1:x+1 2:y+1 3:y-1.
-            // A robot moves only on its own turn, so control c's target is known up front.
-            const uint32_t pz = __shfl_sync(FULL, myv, zc & 31);
-            const int tx = unpack_x(pz) + (u == 1) - (u == 0);
-            const int ty = unpack_y(pz) + (u == 2) - (u == 3);
-            int blocked0 = 1;
-            if (lane < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
-            const uint32_t tv = pack_xy(tx, ty);
-            int moved = 0, ncoll = 0;
-            for (int c = 0; c < N; ++c) {
-                const uint32_t tvc = __shfl_sync(FULL, tv, c);
-                const int blk = __shfl_sync(FULL, blocked0, c);
-                const int z = __shfl_sync(FULL, zc, c);
-                const uint32_t b = __ballot_sync(FULL, lane < N && pv == tvc);
-                if (!blk && b == 0u) {
-                    if (lane == z) pv = tvc;
-                    if (lane == c) moved = 1;
-                } else {
-                    ++ncoll;
-                }
-            }
-            // per-slot reward so far: -collision_penalty, or the start-of-step distance value (:138-139)
-            double rc = 0.0;
-            if (lane < N) {
-                if (!moved) rc = 0.0 - p.cp;
-                else if (p.dist_reward)
-                    rc = 0.0 + (double)dist_value((int)dbuf[(size_t)tx * p.dt_pitch + ty], sm.any_zero, sm.dmax);
-            }
-            // robot i accumulates onto the slot that drove it (r2c, :129)
-            const double racc0_lo = rc;
-            const int hi32 = __shfl_sync(FULL, __double2hiint(racc0_lo), rank & 31);
-            const int lo32 = __shfl_sync(FULL, __double2loint(racc0_lo), rank & 31);
-            double racc = __hiloint2double(hi32, lo32);
-
-            // ---- footprints (:176-201), robots in index order, lanes = footprint rows -------------
-            const int lastbits = L & 31;
-            int cnt_new = 0;
-            for (int i = 0; i < N; ++i) {
-                const uint32_t pi = __shfl_sync(FULL, pv, i);
-                const int xi = unpack_x(pi), yi = unpack_y(pi);
-                const int x = xi - R + lane;
-                uint32_t rel_new = 0, rel_al = 0;
-                if (lane < S && x >= 0 && x < W) {
-                    const int y0 = yi - R, s0 = y0 >> 5, sh = y0 & 31;
-                    const uint64_t m64 = (uint64_t)low_mask(S) << sh;
-#pragma unroll
-                    for (int k = 0; k < 2; ++k) {
-                        const int s = s0 + k;
-                        uint32_t m = k ? (uint32_t)(m64 >> 32) : (uint32_t)m64;
-                        if (s == strips - 1 && lastbits) m &= low_mask(lastbits);
-                        if (!m || s < 0 || s >= strips) continue;
-                        const int w = s * Wp + x;
-                        const uint32_t wl = __ldg(wall + w) & m, walk = ~__ldg(wall + w) & m;
-                        const uint32_t worth = __ldg(tpos + w) & m;
-                        const uint32_t c0 = cov[w], so = seen[w];
-                        const uint32_t nf = walk & ~c0, al = walk & c0;
-                        if (nf) cov[w] = c0 | nf;
-                        if (wl & ~so) seen[w] = so | wl;
-                        cnt_new += __popc(nf);
-                        const uint32_t nfw = nf & worth;
-                        rel_new |= k ? (nfw << (32 - sh)) : (nfw >> sh);
-                        rel_al |= k ? (al << (32 - sh)) : (al >> sh);
-                    }
-                }
-                if (lane < S) sm.rows[i * S + lane] = make_uint2(rel_new, rel_al);
-                __syncwarp();
-            }
-            // float64 accumulation in the reference's raster order (x rows outer, y inner)
-            if (lane < N) {
-                for (int r = 0; r < S; ++r) {
-                    const uint2 rb = sm.rows[lane * S + r];
-                    uint32_t both = rb.x | rb.y;
-                    while (both) {
-                        const uint32_t bit = both & (0u - both);
-                        both ^= bit;
-                        if (rb.x & bit) racc = __dadd_rn(racc, 1.0);                 // += grid[j][k]
-                        else racc = __dsub_rn(racc, p.free_penalty);                 // -= free_penalty
-                    }
-                }
-                // motion_penalty quirk (:203-208): -1 per slot on the very first step
-                if (head->flags & 1u) racc = __dadd_rn(racc, -1.0);
-                sm.rew[rank] = racc;
-            }
-            cnt_new = (int)__reduce_add_sync(FULL, cnt_new);
-            __syncwarp();
-            if (lane < N && pv != myv) hpos[lane] = pv;
-            if (lane == 0) {
-                double r = numpy_sum(sm.rew, N);                                    // :214
-                const int cs = head->currstep + 1;                                  // :211
-                const int covered = hcov[0] + cnt_new;
-                const int fc = __ldg(p.free_counts + map_idx);
-                double th = head->done_thresh;
-                int dn = 0;
-                bool full;                                                         // :215, :401-414
-                if (th >= 1.0) full = covered >= fc;
-                else full = th <= (double)covered / (double)fc;
-                if (full) { r += p.terminal; th += p.done_incr; dn = 1; head->done_thresh = th; }
-                const double epr = head->ep_return + r;
-                head->currstep = cs;
-                head->flags = head->flags & ~1u;
-                head->ep_return = epr;
-                if (cnt_new) hcov[0] = covered;
-                sm.covered = covered;
-                const bool trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
-                sm.stats[4] += (double)ncoll;
-                sm.stats[5] += (double)cnt_new;
-                sm.stats[6] += (double)N;
-                int nr = 0;
-                if (dn || trunc) {
-                    sm.stats[0] += 1.0;
-                    sm.stats[1] += epr;
-                    sm.stats[2] += (double)cs;
-                    sm.stats[3] += (double)covered / (double)fc;
-                    nr = 1;
-                }
-                p.reward[e] = (float)r;
-                if (p.reward64) p.reward64[e] = r;
-                p.done[e] = (uint8_t)dn;
-                sm.again = (nr && p.auto_reset) ? 1 : 0;
-                p.needs_reset[e] = (nr && !p.auto_reset) ? 1 : 0;
-            }
-        } else if (lane == 0) {
-            sm.covered = hcov[0];
-            sm.again = 0;
-            if (mode == MODE_STEP) {                                               // sentinel (:88-90)
-                p.reward[e] = 0.0f;
-                if (p.reward64) p.reward64[e] = 0.0;
-                p.done[e] = 1;
-                sm.again = p.auto_reset ? 1 : 0;
-                p.needs_reset[e] = p.auto_reset ? 0 : 1;
+            for (int j = 0; j < N; ++j)
+                if (__shfl_sync(FULL, rank, j) == lane) zc = j;
+        }
+        // ---- sequential, collision-checked moves (:121-174).  Super table: 0:x-1 1:x+1 2:y+1 3:y-1.
+        // A robot moves only on its own turn, so control c's target is known up front.
+        const uint32_t pz = __shfl_sync(FULL, myv, zc & 31);
+        const int tx = unpack_x(pz) + (u == 1) - (u == 0);
+        const int ty = unpack_y(pz) + (u == 2) - (u == 3);
+        int blocked0 = 1;
+        if (lane < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall, Wp, tx, ty);
+        const uint32_t tv = pack_xy(tx, ty);
+        int moved = 0, ncoll = 0;
+        for (int c = 0; c < N; ++c) {
+            const uint32_t tvc = __shfl_sync(FULL, tv, c);
+            const int blk = __shfl_sync(FULL, blocked0, c);
+            const int z = __shfl_sync(FULL, zc, c);
+            const uint32_t b = __ballot_sync(FULL, lane < N && pv == tvc);
+            if (!blk && b == 0u) {
+                if (lane == z) pv = tvc;
+                if (lane == c) moved = 1;
+            } else {
+                ++ncoll;
             }
         }
-        if (lane < N) sm.pos[lane] = pv;
-    } else if (fresh && threadIdx.x == 0) {
-        sm.again = 0;
-    }
-    __syncthreads();
-    if (sm.again) return true;                                // state comes from the reset pass
+        // per-slot reward so far: -collision_penalty, or the start-of-step distance value (:138-139)
+        double rc = 0.0;
+        if (lane < N) {
+            if (!moved) rc = 0.0 - p.cp;
+            else if (p.dist_reward)
+                rc = 0.0 + (double)dist_value((int)dbuf[(size_t)tx * p.dt_pitch + ty], sm.any_zero, sm.dmax);
+        }
+        // robot i accumulates onto the slot that drove it (r2c, :129)
+        const double racc0_lo = rc;
+        const int hi32 = __shfl_sync(FULL, __double2hiint(racc0_lo), rank & 31);
+        const int lo32 = __shfl_sync(FULL, __double2loint(racc0_lo), rank & 31);
+        double racc = __hiloint2double(hi32, lo32);
 
-    if (sm.covered > 0) {
-        super_transform(cov, p.g, dy, p.dt_pitch, sm);
-    } else if (threadIdx.x == 0) {
-        sm.any_zero = 1;
-        sm.dmax = 0;
+        // ---- footprints (:176-201), robots in index order, lanes = footprint rows -------------
+        const int lastbits = L & 31;
+        int cnt_new = 0;
+        for (int i = 0; i < N; ++i) {
+            const uint32_t pi = __shfl_sync(FULL, pv, i);
+            const int xi = unpack_x(pi), yi = unpack_y(pi);
+            const int x = xi - R + lane;
+            uint32_t rel_new = 0, rel_al = 0;
+            if (lane < S && x >= 0 && x < W) {
+                const int y0 = yi - R, s0 = y0 >> 5, sh = y0 & 31;
+                const uint64_t m64 = (uint64_t)low_mask(S) << sh;
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const int s = s0 + k;
+                    uint32_t m = k ? (uint32_t)(m64 >> 32) : (uint32_t)m64;
+                    if (s == strips - 1 && lastbits) m &= low_mask(lastbits);
+                    if (!m || s < 0 || s >= strips) continue;
+                    const int w = s * Wp + x;
+                    const uint32_t wl = __ldg(wall + w) & m, walk = ~__ldg(wall + w) & m;
+                    const uint32_t worth = __ldg(tpos + w) & m;
+                    const uint32_t c0 = cov[w], so = seen[w];
+                    const uint32_t nf = walk & ~c0, al = walk & c0;
+                    if (nf) cov[w] = c0 | nf;
+                    if (wl & ~so) seen[w] = so | wl;
+                    cnt_new += __popc(nf);
+                    const uint32_t nfw = nf & worth;
+                    rel_new |= k ? (nfw << (32 - sh)) : (nfw >> sh);
+                    rel_al |= k ? (al << (32 - sh)) : (al >> sh);
+                }
+            }
+            if (lane < S) sm.rows[i * S + lane] = make_uint2(rel_new, rel_al);
+            __syncwarp();
+        }
+        // float64 accumulation in the reference's raster order (x rows outer, y inner)
+        if (lane < N) {
+            for (int r = 0; r < S; ++r) {
+                const uint2 rb = sm.rows[lane * S + r];
+                uint32_t both = rb.x | rb.y;
+                while (both) {
+                    const uint32_t bit = both & (0u - both);
+                    both ^= bit;
+                    if (rb.x & bit) racc = __dadd_rn(racc, 1.0);                 // += grid[j][k]
+                    else racc = __dsub_rn(racc, p.free_penalty);                 // -= free_penalty
+                }
+            }
+            // motion_penalty quirk (:203-208): -1 per slot on the very first step
+            if (head->flags & 1u) racc = __dadd_rn(racc, -1.0);
+            sm.rew[rank] = racc;
+        }
+        cnt_new = (int)__reduce_add_sync(FULL, cnt_new);
+        __syncwarp();
+        if (lane < N && pv != myv) hpos[lane] = pv;
+        if (lane == 0) {
+            double r = numpy_sum(sm.rew, N);                                    // :214
+            const int cs = head->currstep + 1;                                  // :211
+            const int covered = hcov[0] + cnt_new;
+            const int fc = __ldg(p.free_counts + map_idx);
+            double th = head->done_thresh;
+            int dn = 0;
+            bool full;                                                         // :215, :401-414
+            if (th >= 1.0) full = covered >= fc;
+            else full = th <= (double)covered / (double)fc;
+            if (full) { r += p.terminal; th += p.done_incr; dn = 1; head->done_thresh = th; }
+            const double epr = head->ep_return + r;
+            head->currstep = cs;
+            head->flags = head->flags & ~1u;
+            head->ep_return = epr;
+            if (cnt_new) hcov[0] = covered;
+            slot.covered = covered;
+            const bool trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
+            sm.stats[4] += (double)ncoll;
+            sm.stats[5] += (double)cnt_new;
+            sm.stats[6] += (double)N;
+            int nr = 0;
+            if (dn || trunc) {
+                sm.stats[0] += 1.0;
+                sm.stats[1] += epr;
+                sm.stats[2] += (double)cs;
+                sm.stats[3] += (double)covered / (double)fc;
+                nr = 1;
+            }
+            p.reward[e] = (float)r;
+            if (p.reward64) p.reward64[e] = r;
+            p.done[e] = (uint8_t)dn;
+            again = (nr && p.auto_reset) ? 1 : 0;
+            p.needs_reset[e] = (nr && !p.auto_reset) ? 1 : 0;
+        }
+    } else if (lane == 0) {
+        slot.covered = hcov[0];
+        if (mode == MODE_STEP) {                                               // sentinel (:88-90)
+            p.reward[e] = 0.0f;
+            if (p.reward64) p.reward64[e] = 0.0;
+            p.done[e] = 1;
+            again = p.auto_reset ? 1 : 0;
+            p.needs_reset[e] = p.auto_reset ? 0 : 1;
+        }
     }
-    __syncthreads();
-    write_state(p, sm, dy, e, cov, seen);
-    return false;
+        if (lane < N) slot.pos[lane] = pv;
+    }
+    again = __shfl_sync(FULL, again, 0);
+    __syncwarp();
+    if (again) super_reset_env(p, slot, e, lane);             // fused auto-reset
 }
 
+// Persistent CTA, software-pipelined over its envs: while warps 1..15 stream the state of env e,
+// warp 0 already resolves the dynamics of the CTA's next env into the other slot, so the serial
+// part of a step (moves, footprints, float64 reward) is hidden behind the HBM-bound writes.
 __global__ void __launch_bounds__(ST, 3)
 super_env_kernel(const SuperParams p, const int dt_cells) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SuperSmem sm;
+    __shared__ EnvSlot slots[2];
     SuperDyn dy;
     dy.red = reinterpret_cast<int*>(smem_raw);
     const int nred = dt_scratch_ints(p.g.L, ST);
@@ -402,23 +404,59 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
     const int head_bytes = ((nred + p.g.W + p.g.L + 2) * 4 + 15) & ~15;
     dy.dbuf = p.dt_scratch ? p.dt_scratch + (size_t)blockIdx.x * dt_cells
                            : reinterpret_cast<uint16_t*>(smem_raw + head_bytes);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 16) {
         const uint32_t t = threadIdx.x;
         sm.lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
                                 (t & 8u) ? 1.0f : 0.0f);
     }
     if (threadIdx.x < MCOV_STATS_LEN) sm.stats[threadIdx.x] = 0.0;
-    __syncthreads();
 
-    for (int e = blockIdx.x; e < p.E; e += gridDim.x) {
-        int m = p.mode;
-        if (m == MODE_RESET) {
-            int act = 1;
-            if (p.mask) act = p.mask[e];
-            else if (p.mask_from_flags) act = p.needs_reset[e];
-            if (!act) continue;                               // CTA-uniform
+    const int mode = p.mode;
+    auto next_env = [&](int e) -> int {                       // next env of this CTA that the call touches
+        for (e += gridDim.x; e < p.E; e += gridDim.x) {
+            if (mode != MODE_RESET) return e;
+            if (p.mask ? p.mask[e] : (p.mask_from_flags ? p.needs_reset[e] : 1)) return e;
         }
-        while (super_pass(p, sm, dy, e, m)) m = MODE_RESET; // fused auto-reset
+        return -1;
+    };
+    // the start-of-step distance map (dist_reward, :117-118) needs the whole CTA before the moves
+    auto produce = [&](int e, EnvSlot& slot) {
+        if (p.dist_reward && mode == MODE_STEP) {
+            const bool sentinel = p.act_fmt == MCOV_ACT_I64_BASE4 &&
+                                  reinterpret_cast<const long long*>(p.actions)[e] == -1;
+            if (!sentinel) super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm);
+        }
+        if (warp == 0) super_dynamics(p, sm, slot, dy, e, mode, lane);
+        __syncthreads();
+    };
+
+    int e = next_env((int)blockIdx.x - (int)gridDim.x);
+    int s = 0;
+    __syncthreads();
+    if (e >= 0) produce(e, slots[0]);
+    while (e >= 0) {
+        const int en = next_env(e);
+        if (slots[s].covered > 0) {
+            super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm);
+        } else {
+            if (threadIdx.x == 0) { sm.any_zero = 1; sm.dmax = 0; }
+            __syncthreads();
+        }
+        if (!p.dist_reward) {
+            if (warp == 0) {
+                if (en >= 0) super_dynamics(p, sm, slots[s ^ 1], dy, en, mode, lane);
+            } else {
+                write_state(p, sm, slots[s], dy, e, 32, ST - 32);
+            }
+            __syncthreads();
+        } else {
+            write_state(p, sm, slots[s], dy, e, 0, ST);
+            __syncthreads();
+            if (en >= 0) produce(en, slots[s ^ 1]);
+        }
+        e = en;
+        s ^= 1;
     }
 
     // ---- episode statistics: CTA row -> last CTA folds all rows (single launch) -------------------
@@ -433,10 +471,10 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
         if (sm.last) {
             __threadfence();
             if (threadIdx.x < MCOV_STATS_LEN) {
-                double s = 0.0;
+                double t = 0.0;
                 for (int r = 0; r < (int)gridDim.x; ++r)
-                    s += __ldcg(p.stats_partial + (size_t)r * MCOV_STATS_LEN + threadIdx.x);
-                p.stats_out[threadIdx.x] = s;
+                    t += __ldcg(p.stats_partial + (size_t)r * MCOV_STATS_LEN + threadIdx.x);
+                p.stats_out[threadIdx.x] = t;
             }
             if (threadIdx.x == 0) *p.counter = 0u;
         }
