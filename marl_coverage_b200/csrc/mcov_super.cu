@@ -27,6 +27,9 @@ namespace mcov {
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
+#ifndef MCOV_SUPER_MINB
+#define MCOV_SUPER_MINB 3                     // resident CTAs per SM the register budget is set for
+#endif
 constexpr int ST = 512;                       // threads per CTA
 constexpr int MAXS = 2 * MCOV_MAX_RADIUS + 1;
 
@@ -392,7 +395,7 @@ __device__ void super_dynamics(const SuperParams& p, SuperSmem& sm, EnvSlot& slo
 // Persistent CTA, software-pipelined over its envs: while warps 1..15 stream the state of env e,
 // warp 0 already resolves the dynamics of the CTA's next env into the other slot, so the serial
 // part of a step (moves, footprints, float64 reward) is hidden behind the HBM-bound writes.
-__global__ void __launch_bounds__(ST, 3)
+__global__ void __launch_bounds__(ST, MCOV_SUPER_MINB)
 super_env_kernel(const SuperParams p, const int dt_cells) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ SuperSmem sm;
@@ -495,7 +498,7 @@ inline SuperShape super_shape(const mcov_env* env) {
     const size_t head = (((size_t)dt_scratch_ints(env->g.L, ST) + env->g.W + env->g.L + 2) * 4 + 15) & ~(size_t)15;
     s.global_dt = bytes + head > 200 * 1024;
     s.smem = head + (s.global_dt ? 0 : ((bytes + 15) / 16 * 16));
-    int per_sm = 3;                                          // __launch_bounds__(ST, 3)
+    int per_sm = 3;                                          // __launch_bounds__(ST, MCOV_SUPER_MINB)
     if (!s.global_dt) {
         const int by_smem = (int)((220 * 1024) / (s.smem + sizeof(SuperSmem) + 1024));
         if (per_sm > by_smem) per_sm = by_smem;
