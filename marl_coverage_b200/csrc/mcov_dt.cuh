@@ -22,32 +22,55 @@ __host__ __device__ inline int dt_pitch_of(const Geometry& g) {
     return 2 * words;
 }
 
-// Shared scratch the transform needs besides the distance buffer: 2 ints + 2 * max(blockDim, L) ints.
-__host__ __device__ inline int dt_scratch_ints(int L, int threads) { return 2 + 2 * (L > threads ? L : threads); }
+// A team = a contiguous range of warps of the CTA that runs the transform together (the whole CTA, or
+// a subset while other warps stream output).  Named barrier `bar` (0 = __syncthreads' barrier; use it
+// only when the team is the whole CTA).
+struct Team {
+    int rank, size, bar;
+    __device__ __forceinline__ void sync() const {
+        asm volatile("bar.sync %0, %1;" :: "r"(bar), "r"(size) : "memory");
+    }
+    __device__ __forceinline__ int any(int pred) const {
+        int r;
+        asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.s32 p, %3, 0;\n\t"
+                     "bar.red.or.pred q, %1, %2, p;\n\tselp.s32 %0, 1, 0, q;\n\t}"
+                     : "=r"(r) : "r"(bar), "r"(size), "r"(pred) : "memory");
+        return r;
+    }
+};
+__device__ __forceinline__ Team whole_cta() { Team t; t.rank = threadIdx.x; t.size = blockDim.x; t.bar = 0; return t; }
+
+// Shared scratch the transform needs besides the distance buffer (ints).
+__host__ __device__ inline int dt_scratch_ints(int L, int threads) {
+    const int lp = (L + 1) / 2;
+    return 2 + 2 * (lp > threads ? lp : threads);
+}
 
 // d[x * pitch + y] = taxicab distance from (x, y) to the nearest ZERO pixel (0 on zero pixels).
 // `zero_word(strip, x)` returns the zero-pixel bits of one plane word (bit b <-> y = 32*strip + b);
 // bits with y >= L must be 0.
 //   pass 1 (along y): closed form on the bit words with clz / ffs — no sequential scan;
-//   pass 2 (along x): min-plus sweep, each column cut into `nch` chunks so that L * nch threads work:
+//   pass 2 (along x): min-plus sweep on PAIRS of columns (two uint16 per 32-bit lane, vminu2 /
+//     saturating vaddus2), each column pair cut into `nch` chunks so that the whole team works:
 //     local forward+backward scan per chunk, chunk-end values combined across chunks (min-plus is
 //     associative: entering a chunk with carry c adds c + offset), then applied in a second sweep.
-// All threads of the CTA must call; `red` is dt_scratch_ints(L, blockDim.x) ints of shared scratch.
+// Every thread of the team must call; `red` is dt_scratch_ints(L, team.size) ints of shared scratch.
 template <class ZeroWord>
-__device__ DtResult l1_transform(ZeroWord zero_word, const Geometry& g, uint16_t* d, int pitch, int* red) {
+__device__ DtResult l1_transform(ZeroWord zero_word, const Geometry& g, uint16_t* d, int pitch, int* red,
+                                 const Team team) {
     constexpr unsigned FULLM = 0xffffffffu;
+    constexpr unsigned INF2 = 0xffffffffu;                   // two DT_INF halves
     const int W = g.W, L = g.L, strips = g.strips;
-    const int T = blockDim.x;
-    if (threadIdx.x == 0) { red[0] = 0; red[1] = 0; }
-    __syncthreads();
+    const int T = team.size, tid = team.rank;
+    if (tid == 0) { red[0] = 0; red[1] = 0; }
     int anyz = 0;
     const int nw = W * strips;
-    for (int idx = threadIdx.x; idx < nw; idx += T) {
+    for (int idx = tid; idx < nw; idx += T) {
         const int s = idx / W, x = idx - s * W;              // x fastest within a strip
         const uint32_t z = zero_word(s, x);
         anyz |= (z != 0u);
         uint32_t* drow = reinterpret_cast<uint32_t*>(d + (size_t)x * pitch + 32 * s);
-        if (z == FULLM) {                                    // common early in an episode: all zero pixels
+        if (z == FULLM) {                                    // all zero pixels (obstacles / not yet covered)
 #pragma unroll
             for (int j = 0; j < 16; ++j) drow[j] = 0u;
             continue;
@@ -76,77 +99,88 @@ __device__ DtResult l1_transform(ZeroWord zero_word, const Geometry& g, uint16_t
             drow[j] = packed;
         }
     }
-    anyz = __syncthreads_or(anyz);
+    anyz = team.any(anyz);
 
     // ---- pass 2 ----------------------------------------------------------------------------------
-    int nch = T / L;
+    const int LP = (L + 1) >> 1;                             // column pairs (pitch is even and > L)
+    const int ph = pitch >> 1;                               // 32-bit words per x row
+    int nch = T / LP;
     if (nch < 1) nch = 1;
     if (nch > W) nch = W;
     const int K = (W + nch - 1) / nch;                       // rows per chunk
-    int* endF = red + 2;                                     // [nch][L] forward value at the chunk's last row
-    int* endB = endF + (L > T ? L : T);                      // [nch][L] backward value at the chunk's first row
-    const int items = L * nch;
-    for (int it = threadIdx.x; it < items; it += T) {
-        const int c = it / L, y = it - c * L;
+    uint32_t* endF = reinterpret_cast<uint32_t*>(red + 2);   // [nch][LP] forward value at the chunk's last row
+    uint32_t* endB = endF + (LP > T ? LP : T);               // [nch][LP] backward value at the chunk's first row
+    const int items = LP * nch;
+    constexpr unsigned ONE2 = 0x00010001u;
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(d);
+    for (int it = tid; it < items; it += T) {
+        const int c = it / LP, yp = it - c * LP;
         const int x0 = c * K, x1 = min(x0 + K, W);
-        uint16_t* col = d + y;
-        int v = DT_INF;
-        for (int xb = x0; xb < x1; xb += 8) {
-            int t[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = (xb + k < x1) ? (int)col[(size_t)(xb + k) * pitch] : DT_INF;
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-                if (xb + k < x1) {
-                    v = min(min(t[k], v + 1), DT_INF);
-                    col[(size_t)(xb + k) * pitch] = (uint16_t)v;
-                }
+        uint32_t* col = d32 + yp;
+        uint32_t v = INF2;
+        int x = x0;
+        for (; x + 4 <= x1; x += 4) {
+            uint32_t t0 = col[(size_t)x * ph], t1 = col[(size_t)(x + 1) * ph];
+            uint32_t t2 = col[(size_t)(x + 2) * ph], t3 = col[(size_t)(x + 3) * ph];
+            v = __vminu2(t0, __vaddus2(v, ONE2)); col[(size_t)x * ph] = v;
+            v = __vminu2(t1, __vaddus2(v, ONE2)); col[(size_t)(x + 1) * ph] = v;
+            v = __vminu2(t2, __vaddus2(v, ONE2)); col[(size_t)(x + 2) * ph] = v;
+            v = __vminu2(t3, __vaddus2(v, ONE2)); col[(size_t)(x + 3) * ph] = v;
         }
-        endF[it] = x1 > x0 ? v : DT_INF;
-        v = DT_INF;
-        for (int xb = x1 - 1; xb >= x0; xb -= 8) {
-            int t[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = (xb - k >= x0) ? (int)col[(size_t)(xb - k) * pitch] : DT_INF;
-#pragma unroll
-            for (int k = 0; k < 8; ++k)
-                if (xb - k >= x0) {
-                    v = min(min(t[k], v + 1), DT_INF);
-                    col[(size_t)(xb - k) * pitch] = (uint16_t)v;
-                }
+        for (; x < x1; ++x) { v = __vminu2(col[(size_t)x * ph], __vaddus2(v, ONE2)); col[(size_t)x * ph] = v; }
+        endF[it] = v;                                        // INF2 for an empty chunk
+        v = INF2;
+        x = x1 - 1;
+        for (; x - 3 >= x0; x -= 4) {
+            uint32_t t0 = col[(size_t)x * ph], t1 = col[(size_t)(x - 1) * ph];
+            uint32_t t2 = col[(size_t)(x - 2) * ph], t3 = col[(size_t)(x - 3) * ph];
+            v = __vminu2(t0, __vaddus2(v, ONE2)); col[(size_t)x * ph] = v;
+            v = __vminu2(t1, __vaddus2(v, ONE2)); col[(size_t)(x - 1) * ph] = v;
+            v = __vminu2(t2, __vaddus2(v, ONE2)); col[(size_t)(x - 2) * ph] = v;
+            v = __vminu2(t3, __vaddus2(v, ONE2)); col[(size_t)(x - 3) * ph] = v;
         }
-        endB[it] = x1 > x0 ? v : DT_INF;
+        for (; x >= x0; --x) { v = __vminu2(col[(size_t)x * ph], __vaddus2(v, ONE2)); col[(size_t)x * ph] = v; }
+        endB[it] = v;
     }
-    __syncthreads();
-    int mx = 0;
-    for (int it = threadIdx.x; it < items; it += T) {
-        const int c = it / L, y = it - c * L;
+    team.sync();
+    uint32_t mx2 = 0;
+    for (int it = tid; it < items; it += T) {
+        const int c = it / LP, yp = it - c * LP;
         const int x0 = c * K, x1 = min(x0 + K, W);
         // carry entering from the left = global forward value at row x0 - 1; from the right likewise
-        int cf = DT_INF, cb = DT_INF;
-        for (int cc = 0; cc < c; ++cc) cf = min(endF[cc * L + y], cf + (min(cc * K + K, W) - cc * K));
+        uint32_t cf = INF2, cb = INF2;
+        for (int cc = 0; cc < c; ++cc) {
+            const uint32_t len = (uint32_t)(min(cc * K + K, W) - cc * K);
+            cf = __vminu2(endF[cc * LP + yp], __vaddus2(cf, len | (len << 16)));
+        }
         for (int cc = nch - 1; cc > c; --cc) {
             const int a0 = cc * K, a1 = min(a0 + K, W);
-            if (a1 > a0) cb = min(endB[cc * L + y], cb + (a1 - a0));
+            if (a1 > a0) {
+                const uint32_t len = (uint32_t)(a1 - a0);
+                cb = __vminu2(endB[cc * LP + yp], __vaddus2(cb, len | (len << 16)));
+            }
         }
-        cf = min(cf, DT_INF);
-        cb = min(cb, DT_INF);
-        uint16_t* col = d + y;
+        uint32_t* col = d32 + yp;
+        const uint32_t keep = (2 * yp + 1 < L) ? 0xffffffffu : 0x0000ffffu;   // odd L: last pair's high half is padding
+        uint32_t up = __vaddus2(cf, ONE2);                                    // cf + (x - x0 + 1)
         for (int x = x0; x < x1; ++x) {
-            int v = (int)col[(size_t)x * pitch];
-            v = min(v, min(cf + (x - x0 + 1), cb + (x1 - x)));
-            v = min(v, DT_INF);
-            col[(size_t)x * pitch] = (uint16_t)v;
-            mx = max(mx, v);
+            const uint32_t k = (uint32_t)(x1 - x);
+            const uint32_t down = __vaddus2(cb, k | (k << 16));               // cb + (x1 - x)
+            uint32_t v = col[(size_t)x * ph];
+            v = __vminu2(v, __vminu2(up, down));
+            col[(size_t)x * ph] = v;
+            mx2 = __vmaxu2(mx2, v & keep);
+            up = __vaddus2(up, ONE2);
         }
     }
+    int mx = (int)max(mx2 & 0xffffu, mx2 >> 16);
     mx = __reduce_max_sync(FULLM, mx);
-    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(&red[1], mx);
-    __syncthreads();
+    if ((tid & 31) == 0 && mx > 0) atomicMax(&red[1], mx);
+    team.sync();
     DtResult r;
     r.any_zero = anyz;
     r.dmax = red[1];
-    __syncthreads();
+    team.sync();
     return r;
 }
 

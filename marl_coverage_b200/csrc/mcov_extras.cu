@@ -82,7 +82,7 @@ dec_extras_kernel(const ExtrasParams p) {
                     [&](int ss, int x) -> uint32_t {
                         const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
                         return plane[ss * Wp + x].x & valid;
-                    }, p.g, dbuf, pitch, red);
+                    }, p.g, dbuf, pitch, red, whole_cta());
                 // max over the PADDED image: edge cells push their distance outwards by `pad`
                 int mx = r.dmax;
                 if (r.any_zero && pad > 0) {

@@ -60,7 +60,7 @@ __device__ void super_transform(const uint32_t* cov, const Geometry& g, const Su
         [&](int ss, int x) -> uint32_t {
             const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
             return ~cov[ss * Wp + x] & valid;
-        }, g, dyn.dbuf, pitch, dyn.red);
+        }, g, dyn.dbuf, pitch, dyn.red, whole_cta());
     if (threadIdx.x == 0) { sm.any_zero = r.any_zero; sm.dmax = r.dmax; }
     if (r.any_zero)
         for (int k = threadIdx.x; k <= r.dmax; k += blockDim.x) dyn.dlut[k] = dist_value(k, 1, r.dmax);

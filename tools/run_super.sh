@@ -1,2 +1,2 @@
-timeout 600 python -m pytest tests/test_super_gpu.py "tests/test_random_gpu.py::test_super_random_vs_oracle" -x -q 2>&1 | tail -3
+timeout 600 python -m pytest tests/test_super_gpu.py tests/test_random_gpu.py "tests/test_dec_gpu.py::test_dec_golden_single_env" -x -q 2>&1 | tail -3
 WORKLOADS=super bash tools/gpu_workloads.sh
