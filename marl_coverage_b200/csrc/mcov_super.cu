@@ -40,6 +40,7 @@ struct SuperSmem {
     uint2 rows[MCOV_MAX_ROBOTS * MAXS];       // per (robot, footprint row): .x new cells worth 1, .y re-covered
     uint32_t pos[MCOV_MAX_ROBOTS];            // poses after the moves
     int any_zero, dmax, covered, again, skip, last;
+    int work;                                 // next unclaimed writer item of the current env
 };
 
 // dynamic shared memory: [dt scratch ints][distance LUT floats: W + L + 2][distance work buffer]
@@ -54,17 +55,17 @@ struct SuperDyn {
 // Also fills the value table dlut[d] = 1 - d / max(d) (float32, super_grid_rl.py:297-303) so that the
 // state writer and the reward lookup never divide.
 __device__ void super_transform(const uint32_t* cov, const Geometry& g, const SuperDyn& dyn, int pitch,
-                                SuperSmem& sm) {
+                                SuperSmem& sm, const Team team) {
     const int Wp = g.Wp, strips = g.strips, lastbits = g.L & 31;
     const DtResult r = l1_transform(
         [&](int ss, int x) -> uint32_t {
             const uint32_t valid = (ss == strips - 1 && lastbits) ? low_mask(lastbits) : FULL;
             return ~cov[ss * Wp + x] & valid;
-        }, g, dyn.dbuf, pitch, dyn.red, whole_cta());
-    if (threadIdx.x == 0) { sm.any_zero = r.any_zero; sm.dmax = r.dmax; }
+        }, g, dyn.dbuf, pitch, dyn.red, team);
+    if (team.rank == 0) { sm.any_zero = r.any_zero; sm.dmax = r.dmax; }
     if (r.any_zero)
-        for (int k = threadIdx.x; k <= r.dmax; k += blockDim.x) dyn.dlut[k] = dist_value(k, 1, r.dmax);
-    __syncthreads();
+        for (int k = team.rank; k <= r.dmax; k += team.size) dyn.dlut[k] = dist_value(k, 1, r.dmax);
+    team.sync();
 }
 
 // np.sum of a float64 vector the way numpy adds it (pairwise_sum with 8 accumulators for n >= 8;
@@ -172,6 +173,96 @@ __device__ void write_state(const SuperParams& p, const SuperSmem& sm, const Env
             }
             __stcs(obs_e + k, v);
         }
+    }
+}
+
+// ---- overlapped schedule (vectorised path) ---------------------------------------------------------
+// The six planes that do not depend on the distance transform (positions, observed obstacles, free)
+// are cut into warp items of IT float4; warps claim items from a shared counter, so the warps that
+// run the transform simply join the writers when they are done.
+constexpr int IT = 128;                                      // float4 per warp item (4 per lane)
+
+__device__ void write_fixed_planes(const SuperParams& p, SuperSmem& sm, const EnvSlot& slot, int e, int lane) {
+    const int N = p.N, W = p.g.W, L = p.g.L, Wp = p.g.Wp;
+    const int WL = W * L, Lq = L >> 2, qp = WL >> 2;
+    const int npos = p.use_scanning ? 1 : N, nz = npos * qp;
+    const int n1 = (nz + IT - 1) / IT, n2 = (qp + IT - 1) / IT;
+    const uint32_t* cov = p.covered + (size_t)e * p.g.PW;
+    const uint32_t* seen = p.seen_obst + (size_t)e * p.g.PW;
+    float* obs_e = p.obs + (size_t)e * p.C * WL;
+    float4* dst = reinterpret_cast<float4*>(obs_e);
+    float4* d_obst = dst + (size_t)nz;
+    float4* d_free = d_obst + qp;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int dx = 32 / Lq, dyq = 32 - dx * Lq;
+    while (true) {
+        int it = 0;
+        if (lane == 0) it = atomicAdd(&sm.work, 1);
+        it = __shfl_sync(FULL, it, 0);
+        if (it >= n1 + n2) break;
+        if (it < n1) {
+            const int base = it * IT;
+#pragma unroll
+            for (int t = 0; t < IT / 32; ++t) {
+                const int q = base + lane + 32 * t;
+                if (q < nz) __stcs(dst + q, z4);
+            }
+            // the lane that zero-filled a robot's float4 patches the 1.0 (same thread: program order)
+            for (int j = 0; j < N; ++j) {
+                const uint32_t pv = slot.pos[j];
+                const int cell = unpack_x(pv) * L + unpack_y(pv);
+                const int plane = p.use_scanning ? 0 : j;
+                const int q = plane * qp + (cell >> 2);
+                if (q >= base && q < base + IT && ((q - base) & 31) == lane)
+                    obs_e[(size_t)plane * WL + cell] = 1.0f;
+            }
+        } else {
+            const int base = (it - n1) * IT;
+            int q = base + lane;
+            int x = q / Lq, yq = q - x * Lq;
+#pragma unroll
+            for (int t = 0; t < IT / 32; ++t) {
+                if (q < qp) {
+                    const int w = (yq >> 3) * Wp + x, nib = (yq & 7) * 4;
+                    const uint32_t so = seen[w], cv = cov[w];
+                    __stcs(d_obst + q, sm.lut[(so >> nib) & 15u]);
+                    __stcs(d_free + q, sm.lut[(~cv >> nib) & 15u]);
+                }
+                q += 32;
+                x += dx;
+                yq += dyq;
+                if (yq >= Lq) { yq -= Lq; ++x; }
+            }
+        }
+    }
+}
+
+// The distance plane, statically split over threads [first, first + nthreads).
+__device__ void write_dist_plane(const SuperParams& p, const SuperSmem& sm, const EnvSlot& slot,
+                                 const SuperDyn& dy, int e, int first, int nthreads) {
+    const int rank = (int)threadIdx.x - first;
+    if (rank < 0 || rank >= nthreads) return;
+    const int W = p.g.W, L = p.g.L, WL = W * L, Lq = L >> 2, qp = WL >> 2, pitch = p.dt_pitch;
+    const int npos = p.use_scanning ? 1 : p.N;
+    const bool flat = slot.covered == 0 || !sm.any_zero || sm.dmax <= 0;
+    const float flat_v = (slot.covered == 0 || sm.any_zero) ? 1.0f : 0.0f;
+    float4* d_dist = reinterpret_cast<float4*>(p.obs + (size_t)e * p.C * WL) + (size_t)(npos + 2) * qp;
+    if (flat) {
+        const float4 fv = make_float4(flat_v, flat_v, flat_v, flat_v);
+        for (int q = rank; q < qp; q += nthreads) __stcs(d_dist + q, fv);
+        return;
+    }
+    const uint16_t* dbuf = dy.dbuf;
+    const float* dlut = dy.dlut;
+    int x = rank / Lq, yq = rank - x * Lq;
+    const int dx = nthreads / Lq, dyq = nthreads - dx * Lq;
+    for (int q = rank; q < qp; q += nthreads) {
+        const uint32_t* dp = reinterpret_cast<const uint32_t*>(dbuf + (size_t)x * pitch + 4 * yq);
+        const uint32_t a = dp[0], b = dp[1];
+        __stcs(d_dist + q, make_float4(dlut[a & 0xffffu], dlut[a >> 16], dlut[b & 0xffffu], dlut[b >> 16]));
+        x += dx;
+        yq += dyq;
+        if (yq >= Lq) { yq -= Lq; ++x; }
     }
 }
 
@@ -428,7 +519,7 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
         if (p.dist_reward && mode == MODE_STEP) {
             const bool sentinel = p.act_fmt == MCOV_ACT_I64_BASE4 &&
                                   reinterpret_cast<const long long*>(p.actions)[e] == -1;
-            if (!sentinel) super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm);
+            if (!sentinel) super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm, whole_cta());
         }
         if (warp == 0) super_dynamics(p, sm, slot, dy, e, mode, lane);
         __syncthreads();
@@ -438,25 +529,49 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
     int s = 0;
     __syncthreads();
     if (e >= 0) produce(e, slots[0]);
+    const bool overlapped = p.vec_ok && !p.dist_reward;
+    constexpr int DT_WARPS = 7;                              // warps 1..7 run the transform, 8..15 write
     while (e >= 0) {
         const int en = next_env(e);
-        if (slots[s].covered > 0) {
-            super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm);
-        } else {
-            if (threadIdx.x == 0) { sm.any_zero = 1; sm.dmax = 0; }
+        if (overlapped) {
+            // warp 0: dynamics of the next env | warps 1..7: transform, then help | warps 8..15: the
+            // six transform-independent planes | then warps 1..15: the distance plane
+            if (threadIdx.x == 0) { sm.work = 0; sm.any_zero = 1; sm.dmax = 0; }
             __syncthreads();
-        }
-        if (!p.dist_reward) {
             if (warp == 0) {
                 if (en >= 0) super_dynamics(p, sm, slots[s ^ 1], dy, en, mode, lane);
             } else {
-                write_state(p, sm, slots[s], dy, e, 32, ST - 32);
+                if (warp <= DT_WARPS && slots[s].covered > 0) {
+                    Team team;
+                    team.rank = (int)threadIdx.x - 32;
+                    team.size = DT_WARPS * 32;
+                    team.bar = 1;
+                    super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm, team);
+                }
+                write_fixed_planes(p, sm, slots[s], e, lane);
+                asm volatile("bar.sync 2, %0;" :: "r"(ST - 32) : "memory");      // transform done, seen by the writers
+                write_dist_plane(p, sm, slots[s], dy, e, 32, ST - 32);
             }
             __syncthreads();
         } else {
-            write_state(p, sm, slots[s], dy, e, 0, ST);
-            __syncthreads();
-            if (en >= 0) produce(en, slots[s ^ 1]);
+            if (slots[s].covered > 0) {
+                super_transform(p.covered + (size_t)e * p.g.PW, p.g, dy, p.dt_pitch, sm, whole_cta());
+            } else {
+                if (threadIdx.x == 0) { sm.any_zero = 1; sm.dmax = 0; }
+                __syncthreads();
+            }
+            if (!p.dist_reward) {
+                if (warp == 0) {
+                    if (en >= 0) super_dynamics(p, sm, slots[s ^ 1], dy, en, mode, lane);
+                } else {
+                    write_state(p, sm, slots[s], dy, e, 32, ST - 32);
+                }
+                __syncthreads();
+            } else {
+                write_state(p, sm, slots[s], dy, e, 0, ST);
+                __syncthreads();
+                if (en >= 0) produce(en, slots[s ^ 1]);
+            }
         }
         e = en;
         s ^= 1;
