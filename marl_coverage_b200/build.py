@@ -32,17 +32,34 @@ def needs_build():
 
 
 def build(force=False, verbose=False):
+    """Compiles every .cu to an object in parallel (one nvcc per file), then links the shared library."""
     if not force and not needs_build():
         return LIB
+    from concurrent.futures import ThreadPoolExecutor
     extra = os.environ.get("MCOV_NVCC_EXTRA", "").split()      # tuning experiments (-DMCOV_SUPER_MINB=2 ...)
-    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]
-    res = subprocess.run(cmd, capture_output=True, text=True)
+    nvcc = _nvcc()
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + extra + (["-Xptxas", "-v"] if verbose else [])
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+
+    def compile_one(src):
+        obj = os.path.join(objdir, src[:-3] + ".o")
+        return obj, subprocess.run([nvcc] + flags + ["-c", os.path.join(CSRC, src), "-o", obj],
+                                   capture_output=True, text=True)
+
+    with ThreadPoolExecutor(len(SOURCES)) as pool:
+        results = list(pool.map(compile_one, SOURCES))
+    for obj, res in results:
+        if res.returncode != 0:
+            sys.stderr.write(res.stdout + res.stderr)
+            raise RuntimeError("nvcc failed building libmcov_b200.so")
+        if verbose:
+            sys.stderr.write(res.stderr)
+    res = subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC"] +
+                         [obj for obj, _ in results] + ["-o", LIB], capture_output=True, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
-        raise RuntimeError("nvcc failed building libmcov_b200.so")
-    if verbose:
-        sys.stderr.write(res.stderr)
+        raise RuntimeError("nvcc failed linking libmcov_b200.so")
     return LIB
 
 

@@ -465,6 +465,7 @@ int mcov_reset(mcov_env* env, const uint8_t* mask_dev, const int32_t* map_idx_de
     if (!obs_out_dev) return fail(MCOV_ERR_NULL, "obs_out is NULL");
     if (!aligned(obs_out_dev, 16)) return fail(MCOV_ERR_ALIGN, "obs_out must be 16-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    env->seed = seed;
     if (env->cfg.env_type == MCOV_ENV_DEC)
         return run_dec(env, mcov::MODE_RESET, nullptr, 0, mask_dev, 0, map_idx_dev, start_xy_dev, seed,
                        obs_out_dev, nullptr, nullptr, nullptr, nullptr, st);
@@ -492,9 +493,10 @@ int mcov_step(mcov_env* env, const void* actions_dev, int action_format, float* 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool dec = env->cfg.env_type == MCOV_ENV_DEC;
     // finished / truncated envs restart in place when auto_reset is on; their obs rows become the
-    // new episode's first observation (gym auto-reset convention).  Seed: constant mixed with the
-    // shard base; the per-slot episode counter and global env id key the draw inside the kernel.
-    const uint64_t seed = 0x9E3779B97F4A7C15ull ^ (uint64_t)env->cfg.env_id_base;
+    // new episode's first observation (gym auto-reset convention).  Seed: derived from the seed of
+    // the last mcov_reset; the per-slot episode counter and the GLOBAL env id key the draw inside
+    // the kernel, so a batch gives the same episodes however it is sharded over GPUs.
+    const uint64_t seed = 0x9E3779B97F4A7C15ull ^ env->seed;
     if (dec)   // DecGridRL: the re-seed is fused into the step kernel (one launch per step)
         return run_dec(env, mcov::MODE_STEP, actions_dev, action_format, nullptr, 0, nullptr, nullptr, seed,
                        obs_out_dev, reward_out_dev, reward64_out_dev, done_out_dev, stats_out_dev, st);

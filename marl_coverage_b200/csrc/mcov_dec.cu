@@ -727,19 +727,29 @@ struct DecLaunchShape {
     int bits_words;
 };
 
-inline int pick_group(const mcov_config& c) {
-    // lanes per env: at least the robots (poses live in lanes), 8 otherwise so that the one-lane
-    // phases (moves, bookkeeping) are shared by 4 envs per warp
-    if (c.num_robots > 16) return 32;
-    if (c.num_robots > 8) return 16;
-    return 8;
+inline int pick_group(const mcov_config& c, int num_sms) {
+    // lanes per env: at least the robots (poses live in lanes).  With many envs 8 lanes per env keep
+    // the one-lane phases (moves, bookkeeping) shared by 4 envs per warp; with few envs (E * G below
+    // the resident thread capacity) wider groups cut the per-env latency instead: a step of 4096
+    // envs is one wave either way, so its duration is the latency of one env pass.
+    int g = 8;
+    if (c.num_robots > 16) g = 32;
+    else if (c.num_robots > 8) g = 16;
+    const long long capacity = (long long)num_sms * 4 * MAX_WARPS * 32;      // resident threads
+    while (g < 32 && (long long)c.num_envs * (2 * g) <= capacity) g *= 2;
+    // MCOV_DEC_GROUP=8|16|32 pins the width (tests run every width on the same traces; tuning)
+    if (const char* f = getenv("MCOV_DEC_GROUP")) {
+        const int v = atoi(f);
+        if ((v == 8 || v == 16 || v == 32) && v >= c.num_robots) g = v;
+    }
+    return g;
 }
 
 inline DecLaunchShape dec_shape(const mcov_env* env) {
     const mcov_config& c = env->cfg;
     const int N = c.num_robots, S = 2 * c.sensor_range + 1, ow = 2 * c.egoradius + 1;
     DecLaunchShape s;
-    s.G = pick_group(c);
+    s.G = pick_group(c, env->num_sms);
     s.bits_words = (N * env->obs_C * ow * ow + 31) / 32 + 1;
     int words = s.bits_words + 3 * N + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 * N * S : 0);
     words = round_up(words, 2);
@@ -801,9 +811,16 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     cudaError_t err;
     const bool plain = p.C == 3;
     // instantiations for the BASELINE configs (C2/C5, C3, C4), generic otherwise
-    if (plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(s, p, st);
-    else if (plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5) err = launch_dec_t<Spec<8, true, 8, 10, 5>>(s, p, st);
-    else if (plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5) err = launch_dec_t<Spec<16, false, 16, 2, 5>>(s, p, st);
+    const bool c2 = plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5;
+    const bool c3 = plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5;
+    const bool c4 = plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5;
+    if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(s, p, st);
+    else if (c2 && s.G == 16) err = launch_dec_t<Spec<16, false, 4, 2, 5>>(s, p, st);
+    else if (c2 && s.G == 32) err = launch_dec_t<Spec<32, false, 4, 2, 5>>(s, p, st);
+    else if (c3 && s.G == 8) err = launch_dec_t<Spec<8, true, 8, 10, 5>>(s, p, st);
+    else if (c3 && s.G == 32) err = launch_dec_t<Spec<32, true, 8, 10, 5>>(s, p, st);
+    else if (c4 && s.G == 16) err = launch_dec_t<Spec<16, false, 16, 2, 5>>(s, p, st);
+    else if (c4 && s.G == 32) err = launch_dec_t<Spec<32, false, 16, 2, 5>>(s, p, st);
     else if (s.G == 8) err = lidar ? launch_dec_t<Spec<8, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<8, false, 0, 0, 0>>(s, p, st);
     else if (s.G == 16) err = lidar ? launch_dec_t<Spec<16, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<16, false, 0, 0, 0>>(s, p, st);
     else err = lidar ? launch_dec_t<Spec<32, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<32, false, 0, 0, 0>>(s, p, st);

@@ -120,6 +120,7 @@ struct mcov_env {
     unsigned char* arena;
     double* beams_dev;        // owned
     int64_t launches;
+    uint64_t seed;            // seed of the last mcov_reset (auto-reset draws derive from it)
     int obs_C;
 };
 

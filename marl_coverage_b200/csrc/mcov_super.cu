@@ -530,7 +530,10 @@ super_env_kernel(const SuperParams p, const int dt_cells) {
     __syncthreads();
     if (e >= 0) produce(e, slots[0]);
     const bool overlapped = p.vec_ok && !p.dist_reward;
-    constexpr int DT_WARPS = 7;                              // warps 1..7 run the transform, 8..15 write
+#ifndef MCOV_SUPER_DTW
+#define MCOV_SUPER_DTW 7
+#endif
+    constexpr int DT_WARPS = MCOV_SUPER_DTW;                 // warps 1..DT_WARPS run the transform, the rest write
     while (e >= 0) {
         const int en = next_env(e);
         if (overlapped) {
