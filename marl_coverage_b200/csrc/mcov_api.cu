@@ -1,5 +1,7 @@
 // mcov_api.cu — extern "C" boundary of libmcov_b200.so (see include/mcov.h).
+#include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -118,6 +120,7 @@ void fill_dec_params(mcov_env* env, mcov::DecParams& p) {
     p.sensor = c.sensor_type;
     p.n_lasers = c.num_lasers;
     p.beams = env->beams_dev;
+    p.lidar_cells = env->lidar_cells_dev;
     p.single_tool = c.single_square_tool;
     p.comm_radius = c.comm_radius;
     p.want_adj = 1;
@@ -238,6 +241,7 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
 int mcov_destroy(mcov_env* env) {
     if (!env) return MCOV_OK;
     if (env->beams_dev) cudaFree(env->beams_dev);
+    if (env->lidar_cells_dev) cudaFree(env->lidar_cells_dev);
     delete env;
     return MCOV_OK;
 }
@@ -253,6 +257,46 @@ int mcov_set_lidar_beams(mcov_env* env, const double* beams_host, int num_lasers
     cudaError_t ce = cudaMemcpy(env->beams_dev, beams_host, sizeof(double) * 3 * num_lasers,
                                 cudaMemcpyHostToDevice);
     if (ce != cudaSuccess) return cuda_fail(ce, "cudaMemcpy(beams)");
+
+    // Integer beam table.  The reference marches cx += xinc in float64 from the robot cell and
+    // truncates (lidar.py:50-56).  For integer starts below 2^15 the accumulated rounding error is
+    // < 1e-10, so whenever every partial sum k*inc stays further than 1e-7 from an integer (or the
+    // increment is itself an integer: exact arithmetic) the visited cells are start + floor(k*inc)
+    // for EVERY start, and the march becomes a table walk.  Otherwise the float64 march stays.
+    if (env->lidar_cells_dev) { cudaFree(env->lidar_cells_dev); env->lidar_cells_dev = nullptr; }
+    const int R = env->cfg.sensor_range;
+    const char* force = getenv("MCOV_LIDAR_FP64");
+    bool ok = !(force && atoi(force) != 0);
+    uint16_t* table = ok ? new (std::nothrow) uint16_t[(size_t)num_lasers * 16] : nullptr;
+    if (!table) ok = false;
+    for (int l = 0; ok && l < num_lasers; ++l) {
+        const double xinc = beams_host[3 * l], yinc = beams_host[3 * l + 1], dinc = beams_host[3 * l + 2];
+        if (!(dinc >= 1.0)) { ok = false; break; }               // steps shorter than a cell: not this sensor
+        const bool xi_exact = xinc == floor(xinc), yi_exact = yinc == floor(yinc);
+        double sx = 0.0, sy = 0.0, dist = 0.0;
+        int k = 0;
+        for (;; ++k) {
+            if (k >= 16) { ok = false; break; }
+            const double fx = floor(sx), fy = floor(sy);
+            const double mx = fmin(sx - fx, fx + 1.0 - sx), my = fmin(sy - fy, fy + 1.0 - sy);
+            if ((!xi_exact && k > 0 && mx < 1e-7) || (!yi_exact && k > 0 && my < 1e-7)) { ok = false; break; }
+            const int dx = (int)fx, dy = (int)fy;
+            if (dx < -R || dx > R || dy < -R || dy > R) { ok = false; break; }
+            table[l * 16 + k] = (uint16_t)((dx + R) | ((dy + R) << 8));
+            if (!(dist < (double)R)) break;                      // this was the end cell (lidar.py:58-65)
+            sx += xinc;
+            sy += yinc;
+            dist += dinc;
+        }
+        for (int j = k + 1; ok && j < 16; ++j) table[l * 16 + j] = 0xffffu;
+    }
+    if (ok) {
+        ce = cudaMalloc(&env->lidar_cells_dev, sizeof(uint16_t) * 16 * num_lasers);
+        if (ce == cudaSuccess)
+            ce = cudaMemcpy(env->lidar_cells_dev, table, sizeof(uint16_t) * 16 * num_lasers, cudaMemcpyHostToDevice);
+        if (ce != cudaSuccess) { delete[] table; return cuda_fail(ce, "cudaMalloc/cudaMemcpy(lidar cells)"); }
+    }
+    delete[] table;
     return MCOV_OK;
 }
 

@@ -336,6 +336,28 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
                 sm.winO[idx] = 0;
             }
             g.sync();
+            if (p.lidar_cells) {
+                // integer beam table (proved start-independent on the host, mcov_set_lidar_beams):
+                // walk the <= 16 window cells of the beam until the first wall
+                const int nl = p.n_lasers;
+                for (int idx = lg; idx < N * nl; idx += G) {
+                    const int i = fast_div(idx, p.l_magic), l = idx - i * nl;
+                    const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
+                    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
+                    const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
+                    const uint32_t* ww = sm.wallW + i * S;
+                    uint32_t* wf = sm.winF + i * S;
+                    uint32_t* wo = sm.winO + i * S;
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
+                        if (cell == 0xffffu) break;
+                        const int rx = (int)(cell & 0xffu), ry = (int)(cell >> 8);
+                        if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
+                        atomicOr(&wf[rx], 1u << ry);
+                    }
+                }
+            } else {
             const double rng = (double)R;
             for (int idx = lg; idx < N * p.n_lasers; idx += G) {
                 const int i = idx / p.n_lasers, l = idx - i * p.n_lasers;
@@ -362,6 +384,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
                     if (walk) atomicOr(&sm.winF[i * S + rx], 1u << ry);
                     else atomicOr(&sm.winO[i * S + rx], 1u << ry);
                 }
+            }
             }
             if (p.single_tool) {
                 g.sync();
@@ -804,6 +827,7 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.rw_magic = magic_for(p.RW);
     p.s_magic = magic_for(p.S);
     p.n_magic = magic_for(p.N);
+    p.l_magic = magic_for(p.n_lasers > 0 ? p.n_lasers : 1);
     const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
     static const int debug = getenv("MCOV_DEBUG") ? atoi(getenv("MCOV_DEBUG")) : 0;
     p.debug = debug;

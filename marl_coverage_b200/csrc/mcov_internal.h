@@ -21,6 +21,8 @@ struct DecParams {
     int sensor;               // MCOV_SENSOR_*
     int n_lasers;
     const double* beams;      // [n_lasers][3] device
+    const uint16_t* lidar_cells;  // [n_lasers][16] window cells of each beam in march order (0xffff ends), or null
+    uint32_t l_magic;         // ceil(2^32 / n_lasers)
     int single_tool, comm_radius, want_adj, dist_reward;
     int maxsteps, truncate_steps, auto_reset;
     int env_id_base;
@@ -119,6 +121,7 @@ struct mcov_env {
     mcov_layout lay;
     unsigned char* arena;
     double* beams_dev;        // owned
+    uint16_t* lidar_cells_dev; // owned; null when the integer beam table could not be proven exact
     int64_t launches;
     uint64_t seed;            // seed of the last mcov_reset (auto-reset draws derive from it)
     int obs_C;

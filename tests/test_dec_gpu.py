@@ -45,3 +45,14 @@ def test_dec_golden_every_group_width(name, group, monkeypatch):
     monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
     tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=37, check_envs=(0, 36))
+
+
+@pytest.mark.parametrize("name", [n for n in DEC_TRACES if "lidar" in n])
+def test_dec_lidar_float64_march_path(name, monkeypatch):
+    """The lidar normally walks an integer beam table proved exact on the host; the float64 DDA
+    march it replaces stays as the fallback and must give the same bits (MCOV_LIDAR_FP64=1)."""
+    from marl_coverage_b200 import VecDecGridRL
+    from gpu_helpers import replay_trace_on_gpu
+    monkeypatch.setenv("MCOV_LIDAR_FP64", "1")
+    tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    replay_trace_on_gpu(tr, VecDecGridRL, num_envs=3, check_envs=(0, 2))
