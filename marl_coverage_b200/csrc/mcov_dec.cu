@@ -758,6 +758,12 @@ inline int pick_group(const mcov_config& c, int num_sms) {
     int g = 8;
     if (c.num_robots > 16) g = 32;
     else if (c.num_robots > 8) g = 16;
+    // heavy envs (many robots x tall windows, e.g. 8 robots x 21-row lidar windows = 168 window rows)
+    // get more lanes so that the row loop stays at <= 6 iterations: measured on C3, 8 -> 32 lanes
+    // takes the step from 0.160 to 0.111 ms
+    const int rad = c.egoradius > c.sensor_range ? c.egoradius : c.sensor_range;
+    const int rows = c.num_robots * (2 * rad + 1);
+    while (g < 32 && rows > 6 * g) g *= 2;
     const long long capacity = (long long)num_sms * 4 * MAX_WARPS * 32;      // resident threads
     while (g < 32 && (long long)c.num_envs * (2 * g) <= capacity) g *= 2;
     // MCOV_DEC_GROUP=8|16|32 pins the width (tests run every width on the same traces; tuning)
@@ -780,20 +786,25 @@ inline DecLaunchShape dec_shape(const mcov_env* env) {
     int stride_words = MCOV_STATS_LEN * 2 + words;
     if (s.G < 32) stride_words = round_up(stride_words, 32) + s.G;
     s.grp_smem = (size_t)stride_words * 4;
-    int groups = MAX_WARPS * 32 / s.G;
-    const int cap = (int)((200 * 1024) / s.grp_smem);
-    if (groups > cap) groups = cap;
+    // CTA size: the one that keeps the most lane groups resident per SM (shared memory is the limit
+    // for lidar windows: 2 x 83 kB CTAs hold 64 groups where 5 x 41 kB CTAs hold 80)
     const int per_warp = 32 / s.G;
-    groups = groups / per_warp * per_warp;
-    if (groups < per_warp) groups = per_warp;
+    int groups = per_warp, per_sm = 1, best = 0;
+    for (int warps = MAX_WARPS; warps >= 1; warps >>= 1) {
+        const int gr = warps * per_warp;
+        size_t sm_bytes = s.grp_smem * gr;
+        if (sm_bytes < (size_t)warps * 32 * 8) sm_bytes = (size_t)warps * 32 * 8;
+        if (sm_bytes > 200 * 1024) continue;
+        int ps = (int)((220 * 1024) / (sm_bytes + 1024));
+        const int by_regs = 4 * MAX_WARPS / warps;           // 64 registers per thread: 1024 threads per SM
+        if (ps > by_regs) ps = by_regs;
+        if (ps > 16) ps = 16;
+        if (ps * gr > best) { best = ps * gr; groups = gr; per_sm = ps; }
+    }
     s.threads = groups * s.G;
     s.smem = s.grp_smem * groups;
     // the statistics fold reuses the CTA's dynamic smem as blockDim doubles
     if (s.smem < (size_t)s.threads * 8) s.smem = (size_t)s.threads * 8;
-    int per_sm = 4;
-    const int by_smem = (int)((220 * 1024) / (s.smem + 1024));
-    if (per_sm > by_smem) per_sm = by_smem;
-    if (per_sm < 1) per_sm = 1;
     int grid = env->num_sms * per_sm;
     const int need = (c.num_envs + groups - 1) / groups;
     if (grid > need) grid = need;
