@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define MCOV_ABI_VERSION 3
+#define MCOV_ABI_VERSION 4
 #define MCOV_MAX_ROBOTS 32       /* base-4 joint actions live in an int64: 31 digits; lanes: 32 */
 #define MCOV_MAX_RADIUS 15       /* sensor range, egoradius, mini_map_rad: windows fit 32 bits  */
 #define MCOV_MAX_LASERS 1024
@@ -180,6 +180,28 @@ int mcov_observe(mcov_env* env, float* obs_out_dev, void* stream);
 
 /* percent_covered() (dec_grid_rl.py:548-552, super_grid_rl.py:416-421): float64 [E]. */
 int mcov_percent_covered(mcov_env* env, double* out_dev, void* stream);
+
+/* Replay-buffer rows for batched rollouts (the consumer right after the env step).
+ * ReplayBuffer.addtransition, Policies/replaybuffer.py:33-48, for the E transitions of one batched
+ * step: row (ptr + e) % capacity of the caller-owned float32 ring arrays
+ *   ring_state / ring_next [capacity][row_floats], ring_action [capacity][act_dim],
+ *   ring_reward / ring_done [capacity]
+ * receives env e's (state, action, reward, next_state, done).  state/next rows are read at
+ * state_dev + e * src_stride_floats (stride >= row_floats: obs[:, 0] can be pushed without a slicing
+ * copy — Utils/utils.py:31 stores state[0]).  actions: uint8 (actions_are_u8) or float32, [E][act_dim].
+ * The caller advances ptr / size (replaybuffer.py:46-48). */
+int mcov_replay_push(const float* state_dev, const float* next_state_dev, int row_floats,
+                     int64_t src_stride_floats, const void* actions_dev, int actions_are_u8, int act_dim,
+                     const float* reward_dev, const uint8_t* done_dev, int num_envs, float* ring_state_dev,
+                     float* ring_next_dev, float* ring_action_dev, float* ring_reward_dev,
+                     float* ring_done_dev, int64_t ptr, int64_t capacity, void* stream);
+
+/* ReplayBuffer.samplebatch gather, Policies/replaybuffer.py:66-72: out_*[b] = ring_*[idx[b]]. */
+int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int act_dim,
+                       const float* ring_state_dev, const float* ring_next_dev, const float* ring_action_dev,
+                       const float* ring_reward_dev, const float* ring_done_dev, float* out_state_dev,
+                       float* out_next_dev, float* out_action_dev, float* out_reward_dev, float* out_done_dev,
+                       void* stream);
 
 /* Number of kernel launches the library has enqueued on this handle (bench.py gpu_launches). */
 int64_t mcov_launch_count(const mcov_env* env);

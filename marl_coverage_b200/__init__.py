@@ -9,6 +9,7 @@ from .maps import MapTable, gridgen, gridload, load_grid_set    # noqa: F401
 from .sensors import LidarSensor, Sensor, SquareSensor          # noqa: F401
 from .vec_env import VecDecGridRL, VecSuperGridRL               # noqa: F401
 from .envs import DecGridRL, SuperGridRL                        # noqa: F401
+from .replay import ReplayBuffer, collect                       # noqa: F401
 
 __all__ = ["DecGridRL", "SuperGridRL", "VecDecGridRL", "VecSuperGridRL", "Sensor", "SquareSensor",
-           "LidarSensor", "Discrete", "Base_Space", "gridload", "gridgen", "load_grid_set", "MapTable"]
+           "LidarSensor", "Discrete", "ReplayBuffer", "collect", "Base_Space", "gridload", "gridgen", "load_grid_set", "MapTable"]

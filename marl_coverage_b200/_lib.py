@@ -10,7 +10,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmcov_b200.so")
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_ROBOTS = 32
 MAX_RADIUS = 15
 STATS_LEN = 8
@@ -26,7 +26,8 @@ STATUS_NAMES = {0: "MCOV_OK", -1: "MCOV_ERR_BAD_CONFIG", -2: "MCOV_ERR_NULL", -3
 EXPORTS = ("mcov_abi_version", "mcov_last_error", "mcov_plane_geometry", "mcov_create",
            "mcov_destroy", "mcov_set_lidar_beams", "mcov_pack_maps", "mcov_set_maps",
            "mcov_state_layout", "mcov_bind_state", "mcov_obs_shape", "mcov_reset", "mcov_step",
-           "mcov_observe", "mcov_percent_covered", "mcov_launch_count")
+           "mcov_observe", "mcov_percent_covered", "mcov_launch_count", "mcov_replay_push",
+           "mcov_replay_gather")
 
 
 class McovConfig(C.Structure):
@@ -86,6 +87,8 @@ def _declare(lib):
     lib.mcov_step.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp]
     lib.mcov_observe.argtypes = [vp, vp, vp]
     lib.mcov_percent_covered.argtypes = [vp, vp, vp]
+    lib.mcov_replay_push.argtypes = [vp, vp, i32, i64, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp, i64, i64, vp]
+    lib.mcov_replay_gather.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.mcov_launch_count.restype = i64
     lib.mcov_launch_count.argtypes = [vp]
     for name in EXPORTS:

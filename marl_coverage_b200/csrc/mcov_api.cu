@@ -571,6 +571,48 @@ int mcov_percent_covered(mcov_env* env, double* out_dev, void* stream) {
     return MCOV_OK;
 }
 
+int mcov_replay_push(const float* state_dev, const float* next_state_dev, int row_floats,
+                     int64_t src_stride_floats, const void* actions_dev, int actions_are_u8, int act_dim,
+                     const float* reward_dev, const uint8_t* done_dev, int num_envs, float* ring_state_dev,
+                     float* ring_next_dev, float* ring_action_dev, float* ring_reward_dev,
+                     float* ring_done_dev, int64_t ptr, int64_t capacity, void* stream) {
+    if (!state_dev || !next_state_dev || !actions_dev || !reward_dev || !done_dev || !ring_state_dev ||
+        !ring_next_dev || !ring_action_dev || !ring_reward_dev || !ring_done_dev)
+        return fail(MCOV_ERR_NULL, "mcov_replay_push: NULL buffer");
+    if (row_floats < 1 || act_dim < 1 || num_envs < 1 || capacity < 1 || src_stride_floats < row_floats)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_replay_push: row %d stride %lld act_dim %d envs %d capacity %lld",
+                    row_floats, (long long)src_stride_floats, act_dim, num_envs, (long long)capacity);
+    if (num_envs > capacity) return fail(MCOV_ERR_BAD_CONFIG, "mcov_replay_push: %d envs > capacity %lld",
+                                         num_envs, (long long)capacity);
+    if (ptr < 0 || ptr >= capacity) return fail(MCOV_ERR_BAD_CONFIG, "mcov_replay_push: ptr %lld", (long long)ptr);
+    cudaError_t ce = mcov::launch_replay_push(
+        state_dev, next_state_dev, row_floats, src_stride_floats,
+        actions_are_u8 ? static_cast<const uint8_t*>(actions_dev) : nullptr,
+        actions_are_u8 ? nullptr : static_cast<const float*>(actions_dev), act_dim, reward_dev, done_dev, num_envs,
+        ring_state_dev, ring_next_dev, ring_action_dev, ring_reward_dev, ring_done_dev, ptr, capacity,
+        static_cast<cudaStream_t>(stream));
+    if (ce != cudaSuccess) return cuda_fail(ce, "replay push launch");
+    return MCOV_OK;
+}
+
+int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int act_dim,
+                       const float* ring_state_dev, const float* ring_next_dev, const float* ring_action_dev,
+                       const float* ring_reward_dev, const float* ring_done_dev, float* out_state_dev,
+                       float* out_next_dev, float* out_action_dev, float* out_reward_dev, float* out_done_dev,
+                       void* stream) {
+    if (!idx_dev || !ring_state_dev || !ring_next_dev || !ring_action_dev || !ring_reward_dev || !ring_done_dev ||
+        !out_state_dev || !out_next_dev || !out_action_dev || !out_reward_dev || !out_done_dev)
+        return fail(MCOV_ERR_NULL, "mcov_replay_gather: NULL buffer");
+    if (batch < 1 || row_floats < 1 || act_dim < 1)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_replay_gather: batch %d row %d act_dim %d", batch, row_floats, act_dim);
+    cudaError_t ce = mcov::launch_replay_gather(
+        reinterpret_cast<const long long*>(idx_dev), batch, row_floats, act_dim, ring_state_dev, ring_next_dev,
+        ring_action_dev, ring_reward_dev, ring_done_dev, out_state_dev, out_next_dev, out_action_dev, out_reward_dev,
+        out_done_dev, static_cast<cudaStream_t>(stream));
+    if (ce != cudaSuccess) return cuda_fail(ce, "replay gather launch");
+    return MCOV_OK;
+}
+
 int64_t mcov_launch_count(const mcov_env* env) { return env ? env->launches : 0; }
 
 }  // extern "C"

@@ -36,6 +36,9 @@ namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MAX_WARPS = 8;
+#ifndef MCOV_DEC_MINB
+#define MCOV_DEC_MINB 4                      // resident 256-thread CTAs per SM the register budget is set for
+#endif
 
 // floor(k / d) for k < 2^26, d <= 64, magic = ceil(2^32 / d)
 __device__ __forceinline__ int fast_div(int k, uint32_t magic) { return (int)__umulhi((uint32_t)k, magic); }
@@ -601,7 +604,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
 }
 
 template <class SP>
-__global__ void __launch_bounds__(MAX_WARPS * 32, 4)
+__global__ void __launch_bounds__(MAX_WARPS * 32, MCOV_DEC_MINB)
 dec_env_kernel(const DecParams p) {
     constexpr int G = SP::G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -796,7 +799,7 @@ inline DecLaunchShape dec_shape(const mcov_env* env) {
         if (sm_bytes < (size_t)warps * 32 * 8) sm_bytes = (size_t)warps * 32 * 8;
         if (sm_bytes > 200 * 1024) continue;
         int ps = (int)((220 * 1024) / (sm_bytes + 1024));
-        const int by_regs = 4 * MAX_WARPS / warps;           // 64 registers per thread: 1024 threads per SM
+        const int by_regs = MCOV_DEC_MINB * MAX_WARPS / warps; // register budget of __launch_bounds__
         if (ps > by_regs) ps = by_regs;
         if (ps > 16) ps = 16;
         if (ps * gr > best) { best = ps * gr; groups = gr; per_sm = ps; }

@@ -139,6 +139,14 @@ cudaError_t launch_stats_reduce(mcov_env* env, const double* partial, int rows, 
                                 cudaStream_t st);
 cudaError_t launch_init_headers(mcov_env* env, cudaStream_t st);
 cudaError_t launch_percent_covered(mcov_env* env, double* out, cudaStream_t st);
+cudaError_t launch_replay_push(const float* state, const float* next_state, int row_floats, long long src_stride,
+                               const uint8_t* act_u8, const float* act_f32, int act_dim, const float* reward,
+                               const uint8_t* done, int E, float* r_state, float* r_next, float* r_action,
+                               float* r_reward, float* r_done, long long ptr, long long capacity, cudaStream_t st);
+cudaError_t launch_replay_gather(const long long* idx, int B, int row_floats, int act_dim, const float* r_state,
+                                 const float* r_next, const float* r_action, const float* r_reward,
+                                 const float* r_done, float* o_state, float* o_next, float* o_action,
+                                 float* o_reward, float* o_done, cudaStream_t st);
 int dec_grid_size(const mcov_env* env);
 int super_grid_size(const mcov_env* env);
 int64_t super_dt_scratch_bytes(const mcov_env* env);   // 0 when the buffer lives in shared memory

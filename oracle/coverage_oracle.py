@@ -642,3 +642,38 @@ class OracleDiscrete:
 
     def sample(self, s=None):
         return np.random.randint(self.num_actions, size=s)
+
+
+# --------------------------------------------------------------------------------------
+# replay buffer rows (Policies/replaybuffer.py:3-72) — the consumer right after the env step
+# --------------------------------------------------------------------------------------
+
+class OracleReplayBuffer:
+    """float32 ring arrays with the reference's write pointer arithmetic (replaybuffer.py:33-48)
+    and index gather (replaybuffer.py:66-72)."""
+
+    def __init__(self, obs_dim, act_dim, size):
+        def shp(d):
+            return (size,) if d is None else ((size, d) if np.isscalar(d) else (size, *d))
+        self._maxsize = size
+        self._size = 0
+        self._ptr = 0
+        self._state = np.zeros(shp(obs_dim), dtype=np.float32)
+        self._action = np.zeros(shp(act_dim), dtype=np.float32)
+        self._reward = np.zeros(size, dtype=np.float32)
+        self._nextstate = np.zeros(shp(obs_dim), dtype=np.float32)
+        self._done = np.zeros(size, dtype=np.float32)
+
+    def addtransition(self, state, action, reward, next_state, done):
+        k = self._ptr
+        self._state[k] = state
+        self._action[k] = action
+        self._reward[k] = reward
+        self._nextstate[k] = next_state
+        self._done[k] = done
+        self._ptr = (self._ptr + 1) % self._maxsize
+        self._size = min(self._size + 1, self._maxsize)
+
+    def gather(self, indices):
+        i = np.asarray(indices)
+        return (self._state[i], self._action[i], self._reward[i], self._nextstate[i], self._done[i])

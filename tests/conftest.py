@@ -17,7 +17,9 @@ def pytest_configure(config):
 def golden_names(kind=None):
     out = []
     for f in sorted(os.listdir(GOLDEN_DIR)):
-        if f.endswith(".npz") and (kind is None or f.startswith(kind + "_")):
+        if not f.endswith(".npz") or not f.startswith(("dec_", "super_")):
+            continue                                   # env traces only (replay_ring.npz is a different fixture)
+        if kind is None or f.startswith(kind + "_"):
             out.append(f[:-4])
     return out
 
