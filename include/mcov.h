@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define MCOV_ABI_VERSION 4
+#define MCOV_ABI_VERSION 5
 #define MCOV_MAX_ROBOTS 32       /* base-4 joint actions live in an int64: 31 digits; lanes: 32 */
 #define MCOV_MAX_RADIUS 15       /* sensor range, egoradius, mini_map_rad: windows fit 32 bits  */
 #define MCOV_MAX_LASERS 1024
@@ -202,6 +202,32 @@ int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int ac
                        const float* ring_reward_dev, const float* ring_done_dev, float* out_state_dev,
                        float* out_next_dev, float* out_action_dev, float* out_reward_dev, float* out_done_dev,
                        void* stream);
+
+/* SuperGrid_Sim.step (Environments/sim_env.py:57-190): stateless one-robot, one-step lookahead for a batch
+ * of (state, action) pairs on a SuperGridRL handle (its config supplies collision_penalty, senseradius,
+ * free_penalty, terminal_reward, dist_reward; its map table supplies `grid`).  The arena is not touched.
+ *   state_dev       float32 [B][4][W][L]: position one-hot, observed obstacles, not-yet-covered, distance
+ *                   channel — a row of the [E,4,W,L] tensor a 1-robot / use_scanning SuperGridRL writes
+ *   actions_dev     uint8 [B], SuperGridRL move mapping 0:x-1 1:x+1 2:y+1 3:y-1
+ *   map_idx_dev     int32 [B] into the bound map table, or NULL (map 0)
+ *   pos_xy_dev      int16 [B][2] robot pose, or NULL: found like np.nonzero(pos_img) (sim_env.py:78)
+ *   done_thresh     SuperGrid_Sim._done_thresh (sim_env.py:42), a property of the simulator object
+ *   next_state_dev  float32 [B][4][W][L]; may equal state_dev: planes are then patched in place (the
+ *                   reference mutates the caller's free / observed planes, sim_env.py:157,169)
+ *   reward_out_dev  float32 [B] / reward64_out_dev float64 [B] (either may be NULL)
+ *   terminal_out_dev uint8 [B] or NULL: the terminal-bonus test of sim_env.py:187 (isTerminal's predicate)
+ * The two defects of the function at the reference HEAD (np.asscalar, the missing `grid` argument of
+ * percent_covered) are read as intended; see oracle/coverage_oracle.py:sim_lookahead. */
+int mcov_sim_step(mcov_env* env, const float* state_dev, const uint8_t* actions_dev, const int32_t* map_idx_dev,
+                  const int16_t* pos_xy_dev, int batch, double done_thresh, float* next_state_dev,
+                  float* reward_out_dev, double* reward64_out_dev, uint8_t* terminal_out_dev, void* stream);
+
+/* render() (super_grid_rl.py:423-463, dec_grid_rl.py:554-616) without the pygame window: uint8 RGB frames
+ * [n_frames][H][Wd][3] of the envs listed in env_ids_dev (int32 [n_frames], NULL = envs 0..n_frames-1):
+ * observed obstacles (200,0,255) + covered (0,225,255) + robots (255,0,0), nearest-neighbour upscale, zero
+ * border to the 1075 canvas, DecGridRL flipped along axis 1.  mcov_render_shape reports (H, Wd). */
+int mcov_render_shape(const mcov_env* env, int32_t* height_out, int32_t* width_out);
+int mcov_render(mcov_env* env, const int32_t* env_ids_dev, int n_frames, uint8_t* rgb_out_dev, void* stream);
 
 /* Number of kernel launches the library has enqueued on this handle (bench.py gpu_launches). */
 int64_t mcov_launch_count(const mcov_env* env);

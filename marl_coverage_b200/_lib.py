@@ -10,7 +10,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmcov_b200.so")
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 MAX_ROBOTS = 32
 MAX_RADIUS = 15
 STATS_LEN = 8
@@ -27,7 +27,7 @@ EXPORTS = ("mcov_abi_version", "mcov_last_error", "mcov_plane_geometry", "mcov_c
            "mcov_destroy", "mcov_set_lidar_beams", "mcov_pack_maps", "mcov_set_maps",
            "mcov_state_layout", "mcov_bind_state", "mcov_obs_shape", "mcov_reset", "mcov_step",
            "mcov_observe", "mcov_percent_covered", "mcov_launch_count", "mcov_replay_push",
-           "mcov_replay_gather")
+           "mcov_replay_gather", "mcov_sim_step", "mcov_render_shape", "mcov_render")
 
 
 class McovConfig(C.Structure):
@@ -89,6 +89,9 @@ def _declare(lib):
     lib.mcov_percent_covered.argtypes = [vp, vp, vp]
     lib.mcov_replay_push.argtypes = [vp, vp, i32, i64, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp, i64, i64, vp]
     lib.mcov_replay_gather.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.mcov_sim_step.argtypes = [vp, vp, vp, vp, vp, i32, C.c_double, vp, vp, vp, vp, vp]
+    lib.mcov_render_shape.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.mcov_render.argtypes = [vp, vp, i32, vp, vp]
     lib.mcov_launch_count.restype = i64
     lib.mcov_launch_count.argtypes = [vp]
     for name in EXPORTS:

@@ -613,6 +613,113 @@ int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int ac
     return MCOV_OK;
 }
 
+int mcov_sim_step(mcov_env* env, const float* state_dev, const uint8_t* actions_dev, const int32_t* map_idx_dev,
+                  const int16_t* pos_xy_dev, int batch, double done_thresh, float* next_state_dev,
+                  float* reward_out_dev, double* reward64_out_dev, uint8_t* terminal_out_dev, void* stream) {
+    if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
+    if (env->cfg.env_type != MCOV_ENV_SUPER)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_sim_step needs a SuperGridRL handle (sim_env.py:21-22)");
+    if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+    if (!state_dev || !actions_dev || !next_state_dev) return fail(MCOV_ERR_NULL, "mcov_sim_step: NULL buffer");
+    if (batch < 1) return fail(MCOV_ERR_BAD_CONFIG, "mcov_sim_step: batch %d", batch);
+    if (!aligned(state_dev, 4) || !aligned(next_state_dev, 4))
+        return fail(MCOV_ERR_ALIGN, "mcov_sim_step: state buffers must be float aligned");
+    const mcov_config& c = env->cfg;
+    mcov::SimParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = batch;
+    p.g = env->g;
+    p.R = c.senseradius;
+    p.dist_reward = c.dist_reward;
+    p.cp = c.collision_penalty;
+    p.terminal = c.terminal_reward;
+    p.free_penalty = c.free_penalty;
+    p.done_thresh = done_thresh;
+    p.wall = env->wall;
+    p.pos = env->pos;
+    p.free_counts = env->free_counts;
+    p.state = state_dev;
+    p.actions = actions_dev;
+    p.map_idx = map_idx_dev;
+    p.pos_xy = pos_xy_dev;
+    p.next_state = next_state_dev;
+    p.reward = reward_out_dev;
+    p.reward64 = reward64_out_dev;
+    p.terminal_out = terminal_out_dev;
+    p.vec_ok = ((env->g.W * env->g.L) % 4 == 0) && aligned(state_dev, 16) && aligned(next_state_dev, 16);
+    cudaError_t ce = mcov::launch_sim_lookahead(p, env->num_sms, static_cast<cudaStream_t>(stream));
+    if (ce != cudaSuccess) return cuda_fail(ce, "sim lookahead launch");
+    env->launches += 1;
+    return MCOV_OK;
+}
+
+static int render_geometry(const mcov_env* env, int* scale, int* h, int* w) {
+    // scaling = max(min(B // W, B // L), 1), B = 1075 (super_grid_rl.py:449) or 1024 (dec_grid_rl.py:583);
+    // copyMakeBorder(image, 0, 1075 - shape[1], 0, 1075 - shape[0]) adds rows by the COLUMN deficit and
+    // columns by the ROW deficit (super_grid_rl.py:452-454, dec_grid_rl.py:587-589)
+    const int base = env->cfg.env_type == MCOV_ENV_DEC ? 1024 : 1075;
+    int s = base / env->g.W < base / env->g.L ? base / env->g.W : base / env->g.L;
+    if (s < 1) s = 1;
+    const int bottom = 1075 - env->g.L * s, right = 1075 - env->g.W * s;
+    if (bottom < 0 || right < 0)
+        return fail(MCOV_ERR_BAD_CONFIG, "map %dx%d does not fit the 1075 canvas (cv2.copyMakeBorder fails too)",
+                    env->g.W, env->g.L);
+    *scale = s;
+    *h = env->g.W * s + bottom;
+    *w = env->g.L * s + right;
+    return MCOV_OK;
+}
+
+int mcov_render_shape(const mcov_env* env, int32_t* height_out, int32_t* width_out) {
+    if (!env || !height_out || !width_out) return fail(MCOV_ERR_NULL, "mcov_render_shape: NULL");
+    if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+    int s, h, w;
+    int rc = render_geometry(env, &s, &h, &w);
+    if (rc != MCOV_OK) return rc;
+    *height_out = h;
+    *width_out = w;
+    return MCOV_OK;
+}
+
+int mcov_render(mcov_env* env, const int32_t* env_ids_dev, int n_frames, uint8_t* rgb_out_dev, void* stream) {
+    int rc = check_ready(env);
+    if (rc != MCOV_OK) return rc;
+    if (!rgb_out_dev) return fail(MCOV_ERR_NULL, "mcov_render: output is NULL");
+    if (n_frames < 1 || (!env_ids_dev && n_frames > env->cfg.num_envs))
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_render: n_frames %d", n_frames);
+    if (!aligned(rgb_out_dev, 4)) return fail(MCOV_ERR_ALIGN, "mcov_render: output must be 4-byte aligned");
+    mcov::RenderParams p;
+    memset(&p, 0, sizeof(p));
+    rc = render_geometry(env, &p.scale, &p.out_h, &p.out_w);
+    if (rc != MCOV_OK) return rc;
+    const mcov_config& c = env->cfg;
+    const mcov_layout& l = env->lay;
+    p.n = n_frames;
+    p.env_ids = env_ids_dev;
+    p.g = env->g;
+    p.env_type = c.env_type;
+    p.N = c.num_robots;
+    p.hdr = env->arena + l.off_hdr;
+    p.hdr_stride = l.hdr_stride;
+    p.off_pos = l.hdr_off_pos;
+    if (c.env_type == MCOV_ENV_DEC) {
+        p.n_shown = c.num_robots;                       // _robot_pos_map holds every robot
+        p.flip = 1;
+        p.plane_a = reinterpret_cast<const uint32_t*>(env->arena + l.off_visited);
+        p.fo = reinterpret_cast<const uint2*>(env->arena + l.off_fo);
+    } else {
+        p.n_shown = c.use_scanning ? c.num_robots : 1;  // get_pos_image()[0] (super_grid_rl.py:442)
+        p.flip = 0;
+        p.plane_a = reinterpret_cast<const uint32_t*>(env->arena + l.off_covered);
+        p.plane_b = reinterpret_cast<const uint32_t*>(env->arena + l.off_seen_obst);
+    }
+    p.out = rgb_out_dev;
+    cudaError_t ce = mcov::launch_render(p, env->num_sms, static_cast<cudaStream_t>(stream));
+    if (ce != cudaSuccess) return cuda_fail(ce, "render launch");
+    env->launches += 1;
+    return MCOV_OK;
+}
+
 int64_t mcov_launch_count(const mcov_env* env) { return env ? env->launches : 0; }
 
 }  // extern "C"

@@ -106,6 +106,41 @@ struct SuperParams {
     int vec_ok;               // L % 4 == 0 and obs 16-byte aligned: float4 stores
 };
 
+// SuperGrid_Sim.step lookahead batch (mcov_aux.cu).
+struct SimParams {
+    int B;
+    Geometry g;
+    int R, dist_reward;
+    double cp, terminal, free_penalty, done_thresh;
+    const uint32_t* wall;
+    const uint32_t* pos;
+    const int32_t* free_counts;
+    const float* state;        // [B][4][W][L]
+    const uint8_t* actions;    // [B]
+    const int32_t* map_idx;    // [B] or null (map 0)
+    const int16_t* pos_xy;     // [B][2] or null (scan the position plane)
+    float* next_state;         // [B][4][W][L]; == state: patch in place
+    float* reward;
+    double* reward64;
+    uint8_t* terminal_out;
+    int vec_ok;
+};
+
+// render() frames (mcov_aux.cu).
+struct RenderParams {
+    int n;
+    const int32_t* env_ids;    // [n] or null (envs 0..n-1)
+    Geometry g;
+    int env_type, N, n_shown;  // n_shown: robots drawn (Super without scanning draws robot 0 only)
+    int scale, out_h, out_w, flip;
+    const unsigned char* hdr;
+    int hdr_stride, off_pos;
+    const uint32_t* plane_a;   // Dec: visited; Super: covered
+    const uint32_t* plane_b;   // Super: seen_obst
+    const uint2* fo;           // Dec: per-robot {free, obst}
+    uint8_t* out;              // [n][out_h][out_w][3]
+};
+
 }  // namespace mcov
 
 struct mcov_env {
@@ -147,6 +182,8 @@ cudaError_t launch_replay_gather(const long long* idx, int B, int row_floats, in
                                  const float* r_next, const float* r_action, const float* r_reward,
                                  const float* r_done, float* o_state, float* o_next, float* o_action,
                                  float* o_reward, float* o_done, cudaStream_t st);
+cudaError_t launch_sim_lookahead(const SimParams& p, int num_sms, cudaStream_t st);
+cudaError_t launch_render(const RenderParams& p, int num_sms, cudaStream_t st);
 int dec_grid_size(const mcov_env* env);
 int super_grid_size(const mcov_env* env);
 int64_t super_dt_scratch_bytes(const mcov_env* env);   // 0 when the buffer lives in shared memory

@@ -104,20 +104,9 @@ class _CompatBase(object):
             return True
         return False
 
-    def _frame(self, layers_rgb, scale_base, flip):
-        """Headless version of render(): same colour rules, nearest-neighbour upscale, 1075 canvas
-        (dec_grid_rl.py:562-591, super_grid_rl.py:431-456); no window."""
-        W, L = self._gridwidth, self._gridlen
-        img = np.zeros((W, L, 3))
-        for mask, rgb in layers_rgb:
-            img += mask[:, :, None].astype(np.float64) * np.asarray(rgb, dtype=np.float64)
-        s = max(min(scale_base // W, scale_base // L), 1)
-        img = np.repeat(np.repeat(img, s, axis=0), s, axis=1)
-        canvas = np.zeros((max(1075, img.shape[0]), max(1075, img.shape[1]), 3))
-        canvas[:img.shape[0], :img.shape[1]] = img
-        if flip:
-            canvas = canvas[:, ::-1]
-        return canvas
+    def _frame(self):
+        """render() without the window: the frame is composed by the CUDA render kernel."""
+        return self._vec.render()[0].cpu().numpy()
 
 
 class DecGridRL(_CompatBase):
@@ -231,10 +220,8 @@ class DecGridRL(_CompatBase):
         return self._padded(self._vec.planes()[1][0])
 
     def render(self):
-        free, obst, vis = self._vec.planes()
-        frame = self._frame([(obst[0].any(axis=0), (200, 0, 255)), (vis[0], (0, 225, 255)),
-                             (self._robot_pos_map > 0, (255, 0, 0))], 1024, flip=True)
-        return frame.astype(np.uint8)
+        # dec_grid_rl.py:554-616 returns pygame.surfarray.array3d(surf): uint8
+        return self._frame()
 
 
 class SuperGridRL(_CompatBase):
@@ -326,6 +313,5 @@ class SuperGridRL(_CompatBase):
         return out
 
     def render(self):
-        cov, seen = self._vec.planes()
-        return self._frame([(seen[0], (200, 0, 255)), (cov[0], (0, 225, 255)),
-                            (self.get_pos_image()[0] > 0, (255, 0, 0))], 1075, flip=False)
+        # super_grid_rl.py:423-463 returns the float64 image it blits
+        return self._frame().astype(np.float64)

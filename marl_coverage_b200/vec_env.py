@@ -171,6 +171,21 @@ class _VecEnv:
             _lib.check(self._lib.mcov_percent_covered(self._handle, out.data_ptr(), self._stream()))
         return out
 
+    def render(self, env_ids=None, out=None):
+        """Headless render() frames (super_grid_rl.py:423-463, dec_grid_rl.py:554-616): uint8 CUDA
+        tensor [n, H, Wd, 3] for the listed envs (None: all), composed from the bit planes on the GPU."""
+        import torch
+        h, w = C.c_int32(), C.c_int32()
+        _lib.check(self._lib.mcov_render_shape(self._handle, C.byref(h), C.byref(w)))
+        ids = None if env_ids is None else self._as_dev(env_ids, torch.int32, (len(env_ids),))
+        n = self.num_envs if ids is None else int(ids.numel())
+        if out is None:
+            out = torch.empty((n, h.value, w.value, 3), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.mcov_render(self._handle, _ptr(ids), n, out.data_ptr(), self._stream()))
+        self._keep_ids = ids
+        return out
+
     @property
     def launch_count(self):
         return int(self._lib.mcov_launch_count(self._handle))

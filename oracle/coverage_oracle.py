@@ -677,3 +677,88 @@ class OracleReplayBuffer:
     def gather(self, indices):
         i = np.asarray(indices)
         return (self._state[i], self._action[i], self._reward[i], self._nextstate[i], self._done[i])
+
+
+# --------------------------------------------------------------------------------------
+# SuperGrid_Sim one-step lookahead (Environments/sim_env.py:57-190) — SURVEY.md §8f rank 3
+# --------------------------------------------------------------------------------------
+
+def sim_lookahead(state4, action, grid, env_config, done_thresh=None):
+    """Stateless one-robot lookahead: (state (4,W,L), action 0..3, grid) -> (next_state, reward).
+
+    Restates ``SuperGrid_Sim.step`` (sim_env.py:57-190).  The reference function is broken at HEAD in
+    two places that the restatement reads the way the surrounding code intends:
+      * ``np.asscalar`` (sim_env.py:146-147) was removed in numpy 1.23 -> ``.item()``;
+      * ``self.percent_covered(state)`` (sim_env.py:187) omits the ``grid`` argument of
+        ``percent_covered(self, state, grid)`` (sim_env.py:248) -> the step's own ``grid``.
+    ``tools/pin_sim_render.py`` runs the reference with exactly those two shims to pin this function.
+    Moves use SuperGridRL's mapping 0:x-1 1:x+1 2:y+1 3:y-1; only obstacles block (isOccupied,
+    sim_env.py:210-228); the distance plane is carried through unchanged (not recomputed); the float64
+    reward is accumulated in the reference's order: move term, then footprint cells in raster order.
+    Unlike the reference this does not mutate ``state4`` (the compat class re-applies that side effect).
+    """
+    c = env_config
+    st = np.array(state4, dtype=np.float64)
+    pos_img, seen, free, dist = st[0], st[1].copy(), st[2].copy(), st[3]
+    xs, ys = np.nonzero(pos_img)
+    if xs.size != 1:
+        raise ValueError("sim lookahead needs exactly one robot in the position plane")
+    x0, y0 = int(xs[0]), int(ys[0])
+    W, L = grid.shape
+    reward = 0.0
+    dx, dy = OracleSuperGridRL.MOVES[int(action)]
+    x, y = x0 + dx, y0 + dy
+    if 0 <= x < W and 0 <= y < L and not grid[x, y] < 0:
+        x0, y0 = x, y
+        if c["dist_reward"]:
+            reward += dist[x, y]
+    else:
+        reward -= c["collision_penalty"]
+    r = c["senseradius"]
+    for j in range(x0 - r, x0 + r + 1):
+        for k in range(y0 - r, y0 + r + 1):
+            if not (0 <= j < W and 0 <= k < L):
+                continue
+            if grid[j][k] >= 0 and free[j][k] == 1:
+                reward += grid[j][k]
+                free[j][k] = 0
+            elif grid[j][k] >= 0 and free[j][k] == 0:
+                reward -= c["free_penalty"]
+            elif grid[j][k] < 0 and seen[j][k] == 0:
+                seen[j][k] = 1
+    new_pos = np.zeros((W, L))
+    new_pos[x0, y0] = 1
+    out = np.stack([new_pos, seen, free, dist], axis=0)
+    thresh = c["done_thresh"] if done_thresh is None else done_thresh
+    if min(thresh, 1) <= np.count_nonzero(free < 1) / np.count_nonzero(grid > 0):
+        reward += c["terminal_reward"]
+    return out, float(reward)
+
+
+# --------------------------------------------------------------------------------------
+# render() frames (super_grid_rl.py:423-463, dec_grid_rl.py:554-616) — SURVEY.md §8f rank 4
+# --------------------------------------------------------------------------------------
+
+def render_frame(seen_obst, covered, robot_map, scale_base, flip):
+    """uint8 frame of the reference's render(): colour sum of the three layers (observed obstacle
+    (200,0,255), covered (0,225,255), robot (255,0,0)), nearest-neighbour upscale by
+    s = max(min(scale_base//W, scale_base//L), 1) (cv2.resize INTER_NEAREST with integer factors =
+    pixel replication), zero border of 1075 - L*s rows at the bottom of axis 0 and 1075 - W*s columns on
+    the right of axis 1 (cv2.copyMakeBorder argument order as written: the two are swapped for
+    non-square maps), DecGridRL additionally flips axis 1 (cv2.flip(image, 1)).  scale_base is 1075
+    for SuperGridRL and 1024 for DecGridRL.  The window (pygame) is left out."""
+    W, L = covered.shape
+    img = np.zeros((W, L, 3))
+    img += np.asarray(seen_obst, dtype=np.float64)[:, :, None] * np.array([200., 0., 255.])
+    img += np.asarray(covered, dtype=np.float64)[:, :, None] * np.array([0., 225., 255.])
+    img += np.asarray(robot_map, dtype=np.float64)[:, :, None] * np.array([255., 0., 0.])
+    s = max(min(scale_base // W, scale_base // L), 1)
+    img = np.repeat(np.repeat(img, s, axis=0), s, axis=1)
+    bottom, right = 1075 - img.shape[1], 1075 - img.shape[0]
+    if bottom < 0 or right < 0:
+        raise ValueError("map too large for the 1075 canvas (cv2.copyMakeBorder would fail)")
+    out = np.zeros((img.shape[0] + bottom, img.shape[1] + right, 3))
+    out[:img.shape[0], :img.shape[1]] = img
+    if flip:
+        out = out[:, ::-1]
+    return np.ascontiguousarray(out).astype(np.uint8)
