@@ -37,7 +37,6 @@ __global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams
     __shared__ int s_pos[2];                   // pose after the move
     __shared__ int s_red[SIM_THREADS / 32];
     __shared__ double s_reward;
-    __shared__ int s_newly;
     __shared__ uint8_t s_cls[SIM_MAX_CELLS];
     __shared__ uint8_t s_val[SIM_MAX_CELLS];   // grid value of a newly covered cell (0 or 1)
 
@@ -53,86 +52,34 @@ __global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams
         const uint32_t* wall = p.wall + (size_t)mi * g.PW;
         const uint32_t* posm = p.pos + (size_t)mi * g.PW;
 
-        // ---- where is the robot: np.nonzero(pos_img) (sim_env.py:78), or the caller's pose ----------
+        // ---- stream the planes first (nothing below depends on the pose): out[0] = 0, out[1..3] = in[1..3];
+        //      count covered cells and find the robot (np.nonzero(pos_img), sim_env.py:78) on the way -------
         if (tid == 0) s_first = p.pos_xy ? (int)p.pos_xy[2 * b] * L + (int)p.pos_xy[2 * b + 1] : 0x7fffffff;
-        __syncthreads();
-        if (!p.pos_xy) {
-            int first = 0x7fffffff;
-            for (int k = tid; k < cells; k += SIM_THREADS)
-                if (__ldg(in + k) != 0.0f) { first = k; break; }        // own stride: ascending
-            first = __reduce_min_sync(0xffffffffu, first);
-            if ((tid & 31) == 0 && first != 0x7fffffff) atomicMin(&s_first, first);   // shared memory
-            __syncthreads();
-        }
-
-        // ---- the move (sim_env.py:92-143) and the footprint classes (sim_env.py:150-170) --------------
-        if (tid == 0) {
-            const int idx = s_first == 0x7fffffff ? 0 : s_first;
-            int x = idx / L, y = idx - x * L;
-            const int a = p.actions[b] & 3;
-            const int nx = x + (a == 0 ? -1 : a == 1 ? 1 : 0);
-            const int ny = y + (a == 2 ? 1 : a == 3 ? -1 : 0);
-            double r = 0.0;
-            if (nx >= 0 && nx < W && ny >= 0 && ny < L && !get_bit(wall, g.Wp, nx, ny)) {
-                x = nx; y = ny;
-                if (p.dist_reward) r += (double)__ldg(in + 3 * (size_t)cells + x * L + y);
-            } else {
-                r -= p.cp;
-            }
-            s_pos[0] = x; s_pos[1] = y;
-            s_reward = r;
-        }
-        __syncthreads();
-        const int px = s_pos[0], py = s_pos[1];
-        for (int k = tid; k < S * S; k += SIM_THREADS) {
-            const int j = px - p.R + k / S, kk = py - p.R + k % S;
-            int cls = CELL_NONE, val = 0;
-            if (j >= 0 && j < W && kk >= 0 && kk < L) {
-                if (!get_bit(wall, g.Wp, j, kk)) {
-                    const float f = __ldg(in + 2 * (size_t)cells + j * L + kk);
-                    if (f == 1.0f) { cls = CELL_NEW; val = get_bit(posm, g.Wp, j, kk); }
-                    else if (f == 0.0f) cls = CELL_AGAIN;
-                } else if (__ldg(in + (size_t)cells + j * L + kk) == 0.0f) {
-                    cls = CELL_OBST;
-                }
-            }
-            s_cls[k] = (uint8_t)cls;
-            s_val[k] = (uint8_t)val;
-        }
-        __syncthreads();
-        if (tid == 0) {              // float64 accumulation in the reference's raster order
-            double r = s_reward;
-            int newly = 0;
-            for (int k = 0; k < S * S; ++k) {
-                const int cls = s_cls[k];
-                if (cls == CELL_NEW) { r += (double)s_val[k]; ++newly; }
-                else if (cls == CELL_AGAIN) r -= p.free_penalty;
-            }
-            s_reward = r;
-            s_newly = newly;
-        }
-
-        // ---- stream the planes: out[0] = 0, out[1..3] = in[1..3]; count covered cells on the way --------
-        int covered = 0;
+        int covered = 0, first = 0x7fffffff;
         if (p.vec_ok) {
             const int q = cells >> 2;
             const float4* in4 = reinterpret_cast<const float4*>(in);
             float4* out4 = reinterpret_cast<float4*>(out);
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (!inplace) {
-                for (int k = tid; k < q; k += SIM_THREADS) {
-                    __stcs(out4 + k, z);
-                    __stcs(out4 + q + k, __ldcs(in4 + q + k));
-                    __stcs(out4 + 3 * q + k, __ldcs(in4 + 3 * q + k));
-                }
-            }
             for (int k = tid; k < q; k += SIM_THREADS) {
-                const float4 v = inplace ? in4[2 * q + k] : __ldcs(in4 + 2 * q + k);
-                covered += (v.x < 1.0f) + (v.y < 1.0f) + (v.z < 1.0f) + (v.w < 1.0f);
-                if (!inplace) __stcs(out4 + 2 * q + k, v);
+                if (!p.pos_xy) {
+                    const float4 v0 = __ldcs(in4 + k);
+                    const int hit = v0.x != 0.f ? 0 : v0.y != 0.f ? 1 : v0.z != 0.f ? 2 : v0.w != 0.f ? 3 : -1;
+                    if (hit >= 0) first = min(first, 4 * k + hit);
+                }
+                const float4 v2 = inplace ? in4[2 * q + k] : __ldcs(in4 + 2 * q + k);
+                covered += (v2.x < 1.0f) + (v2.y < 1.0f) + (v2.z < 1.0f) + (v2.w < 1.0f);
+                if (!inplace) {
+                    const float4 v1 = __ldcs(in4 + q + k), v3 = __ldcs(in4 + 3 * q + k);
+                    __stcs(out4 + k, z);
+                    __stcs(out4 + q + k, v1);
+                    __stcs(out4 + 2 * q + k, v2);
+                    __stcs(out4 + 3 * q + k, v3);
+                }
             }
         } else {
             for (int k = tid; k < cells; k += SIM_THREADS) {
+                if (!p.pos_xy && in[k] != 0.0f) first = min(first, k);
                 const float v = in[2 * (size_t)cells + k];
                 covered += (v < 1.0f);
                 if (!inplace) {
@@ -143,8 +90,49 @@ __global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams
                 }
             }
         }
+        __syncthreads();                                                  // s_first initialised
+        if (!p.pos_xy) {
+            first = __reduce_min_sync(0xffffffffu, first);
+            if ((tid & 31) == 0 && first != 0x7fffffff) atomicMin(&s_first, first);   // shared memory
+        }
         covered = block_sum(covered, s_red);     // barriers inside: the bulk stores precede the patches
 
+        // ---- the move (sim_env.py:92-143) -------------------------------------------------------------
+        if (tid == 0) {
+            const int idx = s_first == 0x7fffffff ? 0 : s_first;
+            int x = idx / L, y = idx - x * L;
+            const int a = p.actions[b] & 3;
+            const int nx = x + (a == 0 ? -1 : a == 1 ? 1 : 0);
+            const int ny = y + (a == 2 ? 1 : a == 3 ? -1 : 0);
+            double r = 0.0;
+            if (nx >= 0 && nx < W && ny >= 0 && ny < L && !get_bit(wall, g.Wp, nx, ny)) {
+                x = nx; y = ny;
+                if (p.dist_reward) r += (double)in[3 * (size_t)cells + x * L + y];
+            } else {
+                r -= p.cp;
+            }
+            s_pos[0] = x; s_pos[1] = y;
+            s_reward = r;
+        }
+        __syncthreads();
+        // ---- footprint classes in the order of the reference's if / elif chain (sim_env.py:150-170) ------
+        const int px = s_pos[0], py = s_pos[1];
+        for (int k = tid; k < S * S; k += SIM_THREADS) {
+            const int j = px - p.R + k / S, kk = py - p.R + k % S;
+            int cls = CELL_NONE, val = 0;
+            if (j >= 0 && j < W && kk >= 0 && kk < L) {
+                if (!get_bit(wall, g.Wp, j, kk)) {
+                    const float f = in[2 * (size_t)cells + j * L + kk];
+                    if (f == 1.0f) { cls = CELL_NEW; val = get_bit(posm, g.Wp, j, kk); }
+                    else if (f == 0.0f) cls = CELL_AGAIN;
+                } else if (in[(size_t)cells + j * L + kk] == 0.0f) {
+                    cls = CELL_OBST;
+                }
+            }
+            s_cls[k] = (uint8_t)cls;
+            s_val[k] = (uint8_t)val;
+        }
+        __syncthreads();
         // ---- patches: <= (2r+1)^2 cells and the pose ---------------------------------------------------
         for (int k = tid; k < S * S; k += SIM_THREADS) {
             const int cls = s_cls[k];
@@ -155,13 +143,19 @@ __global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams
             }
         }
         if (tid == 0) {
+            double r = s_reward;         // float64 accumulation in the reference's raster order
+            int newly = 0;
+            for (int k = 0; k < S * S; ++k) {
+                const int cls = s_cls[k];
+                if (cls == CELL_NEW) { r += (double)s_val[k]; ++newly; }
+                else if (cls == CELL_AGAIN) r -= p.free_penalty;
+            }
             if (inplace && s_first != 0x7fffffff) out[s_first] = 0.0f;
             out[px * L + py] = 1.0f;
             // percent_covered (sim_env.py:248-259) and the terminal bonus (sim_env.py:187-188)
             const int total = __ldg(p.free_counts + mi);
-            const double pct = (double)(covered + s_newly) / (double)total;
+            const double pct = (double)(covered + newly) / (double)total;
             const bool term = fmin(p.done_thresh, 1.0) <= pct;
-            double r = s_reward;
             if (term) r += p.terminal;
             if (p.reward64) p.reward64[b] = r;
             if (p.reward) p.reward[b] = (float)r;
@@ -175,60 +169,76 @@ __global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams
 // render
 // ------------------------------------------------------------------------------------------------------
 
-__device__ __forceinline__ uint32_t render_byte(const RenderParams& p, int e, int pixel, int ch) {
-    const int i = pixel / p.out_w;
-    int j = pixel - i * p.out_w;
-    if (p.flip) j = p.out_w - 1 - j;                     // cv2.flip(image, 1), dec_grid_rl.py:593
-    if (i >= p.g.W * p.scale || j >= p.g.L * p.scale) return 0u;     // copyMakeBorder zeros
-    const int x = i / p.scale, y = j / p.scale;          // INTER_NEAREST with an integer factor
-    const int w = (y >> 5) * p.g.Wp + x;
-    const uint32_t bit = 1u << (y & 31);
-    uint32_t obst = 0, cov = 0;
-    if (p.env_type == MCOV_ENV_DEC) {
-        cov = p.plane_a[(size_t)e * p.g.PW + w] & bit;                   // _visited
-        const uint2* fo = p.fo + (size_t)e * p.N * p.g.PW;
-        for (int r = 0; r < p.N; ++r) obst |= fo[(size_t)r * p.g.PW + w].y & bit;   // union of obst_i
-    } else {
-        cov = p.plane_a[(size_t)e * p.g.PW + w] & bit;                   // 1 - _free
-        obst = p.plane_b[(size_t)e * p.g.PW + w] & bit;                  // _observed_obstacles
+// Work item = (frame f, cell row x): the s output rows i in [x*s, x*s+s) are identical (INTER_NEAREST with
+// an integer factor replicates pixels), so the L cell colours of the row are composed once into shared
+// memory and then expanded through a per-column cell table that is the same for every row of every frame.
+// Item x == W is the zero border below the map (copyMakeBorder).  Rows are written as 32-bit words of the
+// flat byte stream (row starts are not 4-byte aligned in general: head / tail bytes go out singly).
+constexpr int RENDER_THREADS = 256;
+
+__device__ __forceinline__ void render_store_row(uint8_t* out, long long row_start, int row_bytes,
+                                                 const uint16_t* ymap, const uint8_t* col, bool zero) {
+    const int head = (int)((4 - (row_start & 3)) & 3);
+    auto byte_at = [&](int r) -> uint32_t {
+        if (zero) return 0u;
+        const int j = r / 3, ch = r - 3 * j;
+        const uint32_t c = ymap[j];
+        return c == 0xffffu ? 0u : (uint32_t)col[c * 3 + ch];
+    };
+    for (int r = threadIdx.x; r < head && r < row_bytes; r += RENDER_THREADS) out[row_start + r] = (uint8_t)byte_at(r);
+    const int words = (row_bytes - head) >> 2;
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(out + row_start + head);
+    for (int w = threadIdx.x; w < words; w += RENDER_THREADS) {
+        const int r = head + 4 * w;
+        const uint32_t v = byte_at(r) | (byte_at(r + 1) << 8) | (byte_at(r + 2) << 16) | (byte_at(r + 3) << 24);
+        __stcs(out32 + w, v);
     }
-    const int16_t* pos = reinterpret_cast<const int16_t*>(p.hdr + (size_t)e * p.hdr_stride + p.off_pos);
-    uint32_t robot = 0;
-    for (int r = 0; r < p.n_shown; ++r) robot |= (pos[2 * r] == x && pos[2 * r + 1] == y);
-    uint32_t v;
-    if (ch == 0) v = (obst ? 200u : 0u) + (robot ? 255u : 0u);
-    else if (ch == 1) v = cov ? 225u : 0u;
-    else v = (obst ? 255u : 0u) + (cov ? 255u : 0u);
-    return v & 0xffu;
+    for (int r = head + 4 * words + threadIdx.x; r < row_bytes; r += RENDER_THREADS)
+        out[row_start + r] = (uint8_t)byte_at(r);
 }
 
-__global__ void __launch_bounds__(256) render_kernel(RenderParams p) {
-    const long long frame_bytes = (long long)p.out_h * p.out_w * 3;
-    const long long total = frame_bytes * p.n;
-    const long long words = total >> 2;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    uint32_t* out32 = reinterpret_cast<uint32_t*>(p.out);
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < words; t += stride) {
-        const long long b0 = t << 2;
-        int f = (int)(b0 / frame_bytes);
-        int r = (int)(b0 - (long long)f * frame_bytes);
-        uint32_t word = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            if (r >= frame_bytes) { r = 0; ++f; }
-            const int e = p.env_ids ? p.env_ids[f] : f;
-            const int pixel = r / 3;
-            word |= render_byte(p, e, pixel, r - pixel * 3) << (8 * k);
-            ++r;
-        }
-        __stcs(out32 + t, word);
+__global__ void __launch_bounds__(RENDER_THREADS) render_kernel(RenderParams p) {
+    extern __shared__ __align__(16) unsigned char rsm[];
+    uint16_t* ymap = reinterpret_cast<uint16_t*>(rsm);                     // [out_w] column -> cell y (0xffff: border)
+    uint8_t* col = rsm + ((2 * p.out_w + 15) & ~15);                       // [L][3] colours of the current cell row
+    const int W = p.g.W, L = p.g.L, s = p.scale;
+    for (int j = threadIdx.x; j < p.out_w; j += RENDER_THREADS) {
+        const int jj = p.flip ? p.out_w - 1 - j : j;                       // cv2.flip(image, 1), dec_grid_rl.py:593
+        ymap[j] = jj < L * s ? (uint16_t)(jj / s) : (uint16_t)0xffffu;
     }
-    if (blockIdx.x == 0 && threadIdx.x < (int)(total & 3)) {     // <= 3 tail bytes
-        const long long b = (words << 2) + threadIdx.x;
-        const int f = (int)(b / frame_bytes);
-        const int r = (int)(b - (long long)f * frame_bytes);
+    const int row_bytes = p.out_w * 3;
+    const int items = p.n * (W + 1);
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int f = item / (W + 1), x = item - f * (W + 1);
         const int e = p.env_ids ? p.env_ids[f] : f;
-        p.out[b] = (uint8_t)render_byte(p, e, r / 3, r % 3);
+        const long long frame0 = (long long)f * p.out_h * row_bytes;
+        __syncthreads();                                                   // ymap ready / previous col consumed
+        if (x == W) {
+            for (int i = W * s; i < p.out_h; ++i) render_store_row(p.out, frame0 + (long long)i * row_bytes, row_bytes, ymap, col, true);
+            continue;
+        }
+        const int16_t* pos = reinterpret_cast<const int16_t*>(p.hdr + (size_t)e * p.hdr_stride + p.off_pos);
+        for (int y = threadIdx.x; y < L; y += RENDER_THREADS) {
+            const int w = (y >> 5) * p.g.Wp + x;
+            const uint32_t bit = 1u << (y & 31);
+            uint32_t obst = 0, cov;
+            if (p.env_type == MCOV_ENV_DEC) {
+                cov = p.plane_a[(size_t)e * p.g.PW + w] & bit;                           // _visited
+                const uint2* fo = p.fo + (size_t)e * p.N * p.g.PW;
+                for (int r = 0; r < p.N; ++r) obst |= fo[(size_t)r * p.g.PW + w].y & bit;   // union of obst_i
+            } else {
+                cov = p.plane_a[(size_t)e * p.g.PW + w] & bit;                           // 1 - _free
+                obst = p.plane_b[(size_t)e * p.g.PW + w] & bit;                          // _observed_obstacles
+            }
+            uint32_t robot = 0;
+            for (int r = 0; r < p.n_shown; ++r) robot |= (pos[2 * r] == x && pos[2 * r + 1] == y);
+            col[3 * y + 0] = (uint8_t)((obst ? 200u : 0u) + (robot ? 255u : 0u));
+            col[3 * y + 1] = (uint8_t)(cov ? 225u : 0u);
+            col[3 * y + 2] = (uint8_t)((obst ? 255u : 0u) + (cov ? 255u : 0u));
+        }
+        __syncthreads();
+        for (int i = x * s; i < x * s + s; ++i)
+            render_store_row(p.out, frame0 + (long long)i * row_bytes, row_bytes, ymap, col, false);
     }
 }
 
@@ -242,12 +252,11 @@ cudaError_t launch_sim_lookahead(const SimParams& p, int num_sms, cudaStream_t s
 }
 
 cudaError_t launch_render(const RenderParams& p, int num_sms, cudaStream_t st) {
-    const long long words = ((long long)p.out_h * p.out_w * 3 * p.n) >> 2;
-    long long grid = (words + 255) / 256;
-    const long long cap = (long long)num_sms * 16;
-    if (grid > cap) grid = cap;
-    if (grid < 1) grid = 1;
-    render_kernel<<<(int)grid, 256, 0, st>>>(p);
+    const int items = p.n * (p.g.W + 1);
+    int grid = num_sms * 8;
+    if (grid > items) grid = items;
+    const size_t smem = ((2 * (size_t)p.out_w + 15) & ~(size_t)15) + 3 * (size_t)p.g.L;
+    render_kernel<<<grid, RENDER_THREADS, smem, st>>>(p);
     return cudaGetLastError();
 }
 

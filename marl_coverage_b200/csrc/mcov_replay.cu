@@ -21,14 +21,22 @@ replay_push_kernel(const VT* __restrict__ state, const VT* __restrict__ next_sta
                    const float* __restrict__ reward, const uint8_t* __restrict__ done, int E,
                    VT* __restrict__ r_state, VT* __restrict__ r_next, float* __restrict__ r_action,
                    float* __restrict__ r_reward, float* __restrict__ r_done, long long ptr, long long capacity) {
-    const long long total = (long long)E * row;
+    // one warp per transition row: no per-element division, 8 independent 4/16-byte loads in flight per lane
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
-        const int e = (int)(k / row);
-        const int c = (int)(k - (long long)e * row);
-        const long long dst = ((ptr + e) % capacity) * row + c;
-        __stcs(r_state + dst, __ldcs(state + e * src_stride + c));
-        __stcs(r_next + dst, __ldcs(next_state + e * src_stride + c));
+    const int lane = threadIdx.x & 31, nwarps = (int)(stride >> 5);
+    for (int e = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5); e < E; e += nwarps) {
+        const VT* s0 = state + e * src_stride;
+        const VT* s1 = next_state + e * src_stride;
+        const long long dst = ((ptr + e) % capacity) * row;
+        for (int c = lane; c < row; c += 128) {
+            VT a[4], b[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c + 32 * u < row) { a[u] = __ldcs(s0 + c + 32 * u); b[u] = __ldcs(s1 + c + 32 * u); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c + 32 * u < row) { __stcs(r_state + dst + c + 32 * u, a[u]); __stcs(r_next + dst + c + 32 * u, b[u]); }
+        }
     }
     const long long small = (long long)E * act_dim;
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < small; k += stride) {
@@ -50,14 +58,19 @@ replay_gather_kernel(const long long* __restrict__ idx, int B, int row, int act_
                      const float* __restrict__ r_action, const float* __restrict__ r_reward,
                      const float* __restrict__ r_done, VT* __restrict__ o_state, VT* __restrict__ o_next,
                      float* __restrict__ o_action, float* __restrict__ o_reward, float* __restrict__ o_done) {
-    const long long total = (long long)B * row;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
-        const int b = (int)(k / row);
-        const int c = (int)(k - (long long)b * row);
-        const long long src = idx[b] * row + c;
-        __stcs(o_state + k, __ldg(r_state + src));
-        __stcs(o_next + k, __ldg(r_next + src));
+    const int lane = threadIdx.x & 31, nwarps = (int)(stride >> 5);
+    for (int b = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5); b < B; b += nwarps) {
+        const long long src = idx[b] * row, dst = (long long)b * row;
+        for (int c = lane; c < row; c += 128) {
+            VT a[4], d[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c + 32 * u < row) { a[u] = __ldg(r_state + src + c + 32 * u); d[u] = __ldg(r_next + src + c + 32 * u); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c + 32 * u < row) { __stcs(o_state + dst + c + 32 * u, a[u]); __stcs(o_next + dst + c + 32 * u, d[u]); }
+        }
     }
     const long long small = (long long)B * act_dim;
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < small; k += stride) {
@@ -93,12 +106,12 @@ cudaError_t launch_replay_push(const float* state, const float* next_state, int 
                      al16(r_state) && al16(r_next);
     if (vec) {
         const int row = row_floats / 4;
-        replay_push_kernel<float4><<<grid_for((long long)E * row), 256, 0, st>>>(
+        replay_push_kernel<float4><<<grid_for((long long)E * 32), 256, 0, st>>>(
             reinterpret_cast<const float4*>(state), reinterpret_cast<const float4*>(next_state), row, src_stride / 4,
             act_u8, act_f32, act_dim, reward, done, E, reinterpret_cast<float4*>(r_state),
             reinterpret_cast<float4*>(r_next), r_action, r_reward, r_done, ptr, capacity);
     } else {
-        replay_push_kernel<float><<<grid_for((long long)E * row_floats), 256, 0, st>>>(
+        replay_push_kernel<float><<<grid_for((long long)E * 32), 256, 0, st>>>(
             state, next_state, row_floats, src_stride, act_u8, act_f32, act_dim, reward, done, E, r_state, r_next,
             r_action, r_reward, r_done, ptr, capacity);
     }
@@ -112,12 +125,12 @@ cudaError_t launch_replay_gather(const long long* idx, int B, int row_floats, in
     const bool vec = row_floats % 4 == 0 && al16(r_state) && al16(r_next) && al16(o_state) && al16(o_next);
     if (vec) {
         const int row = row_floats / 4;
-        replay_gather_kernel<float4><<<grid_for((long long)B * row), 256, 0, st>>>(
+        replay_gather_kernel<float4><<<grid_for((long long)B * 32), 256, 0, st>>>(
             idx, B, row, act_dim, reinterpret_cast<const float4*>(r_state), reinterpret_cast<const float4*>(r_next),
             r_action, r_reward, r_done, reinterpret_cast<float4*>(o_state), reinterpret_cast<float4*>(o_next),
             o_action, o_reward, o_done);
     } else {
-        replay_gather_kernel<float><<<grid_for((long long)B * row_floats), 256, 0, st>>>(
+        replay_gather_kernel<float><<<grid_for((long long)B * 32), 256, 0, st>>>(
             idx, B, row_floats, act_dim, r_state, r_next, r_action, r_reward, r_done, o_state, o_next, o_action,
             o_reward, o_done);
     }
