@@ -386,38 +386,67 @@ def run_gpu(args):
             "peak_source": peak_src}
     del envk
 
-    # ---- e2e: host buffers through the public API: pinned host actions -> H2D, step,
-    # reward/done/stats -> D2H, synchronised every step (the caller reads them) -------------------
+    # ---- e2e: host buffers through the public API, every step: pinned host actions -> H2D, step,
+    # reward/done/stats -> D2H.  Double-buffered on two copy streams; the host waits for (= consumes) the
+    # results of step t-1 while step t runs, as a rollout loop whose policy lives on the GPU does -------
     acts_host = acts.cpu().pin_memory()
-    act_dev = torch.empty((E, N), dtype=torch.uint8, device=device)
-    rew_host = torch.empty((E,), dtype=torch.float32).pin_memory()
-    done_host = torch.empty((E,), dtype=torch.uint8).pin_memory()
-    stats_host = torch.empty((8,), dtype=torch.float64).pin_memory()
+    act_dev = [torch.empty((E, N), dtype=torch.uint8, device=device) for _ in range(2)]
+    res = [env.make_result_buffers() for _ in range(2)]
+    host = [{"reward": torch.empty((E,), dtype=torch.float32).pin_memory(),
+             "done": torch.empty((E,), dtype=torch.uint8).pin_memory(),
+             "stats": torch.empty((8,), dtype=torch.float64).pin_memory()} for _ in range(2)]
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    ev_in = [torch.cuda.Event() for _ in range(2)]
+    ev_step = [torch.cuda.Event() for _ in range(2)]
+    ev_out = [torch.cuda.Event() for _ in range(2)]
+    for ev in ev_step + ev_out:
+        ev.record(main)
     Ke = min(K, 200)
-    for k in range(3):
-        act_dev.copy_(acts_host[k % T], non_blocking=True)
-        env.step(act_dev, want_stats=True)
+    host_sum = 0.0
+
+    def e2e_step(k):
+        b = k & 1
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_step[b])                  # step k-2 has consumed act_dev[b]
+            act_dev[b].copy_(acts_host[k % T], non_blocking=True)
+            ev_in[b].record(s_in)
+        main.wait_event(ev_in[b])
+        main.wait_event(ev_out[b])                       # step k-2's results have left res[b]
+        env.step(act_dev[b], want_stats=True, results=res[b])
+        ev_step[b].record(main)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_step[b])
+            host[b]["reward"].copy_(res[b]["reward"], non_blocking=True)
+            host[b]["done"].copy_(res[b]["done"], non_blocking=True)
+            host[b]["stats"].copy_(res[b]["stats"], non_blocking=True)
+            ev_out[b].record(s_out)
+
+    for k in range(4):
+        e2e_step(k)
     torch.cuda.synchronize(device)
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(main)
     for k in range(Ke):
-        act_dev.copy_(acts_host[k % T], non_blocking=True)
-        _, r, d = env.step(act_dev, want_stats=True)
-        rew_host.copy_(r, non_blocking=True)
-        done_host.copy_(d, non_blocking=True)
-        stats_host.copy_(env.stats, non_blocking=True)
-        main.synchronize()
+        e2e_step(k)
+        if k >= 1:
+            ev_out[(k - 1) & 1].synchronize()            # the caller reads step k-1's results here
+            host_sum += float(host[(k - 1) & 1]["stats"][6])
+    ev_out[(Ke - 1) & 1].synchronize()
+    host_sum += float(host[(Ke - 1) & 1]["stats"][6])
+    main.wait_stream(s_out)
     e1.record(main)
     torch.cuda.synchronize(device)
+    assert host_sum == float(Ke) * E * N, "e2e: host did not see every step's statistics"
     te = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e = {"value": world * E * N * Ke / (float(te.item()) * 1e-3), "unit": UNIT,
            "h2d_bytes_per_step": E * N, "d2h_bytes_per_step": E * 4 + E + 64,
-           "note": "observations stay in HBM for the policy; actions H2D, reward/done/stats D2H, "
-                   "host sync every step"}
+           "note": "observations stay in HBM for the policy; per step: actions H2D from pinned memory, "
+                   "reward/done/stats D2H; double-buffered on copy streams, the host reads step t-1's "
+                   "results while step t runs"}
 
     if rank == 0 and world == 1 and args.workload == "c5" and not args.no_extras:
         c2_extra = run_c2_extra(torch, device)

@@ -123,15 +123,31 @@ class _VecEnv:
         self._keep = (mi, sx, mk)           # keep inputs alive until the stream has consumed them
         return obs
 
-    def step(self, actions, out=None, want_stats=False):
+    def make_result_buffers(self):
+        """A second set of per-step outputs for ``step(results=...)``: lets a caller double-buffer the
+        device->host read of step t against the kernel of step t+1."""
+        import torch
+        E = self.num_envs
+        return {"reward": torch.zeros((E,), dtype=torch.float32, device=self.device),
+                "reward64": torch.zeros((E,), dtype=torch.float64, device=self.device),
+                "done": torch.zeros((E,), dtype=torch.uint8, device=self.device),
+                "stats": torch.zeros((_lib.STATS_LEN,), dtype=torch.float64, device=self.device)}
+
+    def step(self, actions, out=None, want_stats=False, results=None):
         """One transition of every env.
 
         actions: uint8 [E, N] per-robot moves (0..3) or int64 [E] base-4 joint actions (the
         reference's integer form; -1 = sentinel).  CUDA tensors are used as they are; host
         tensors/arrays are copied to the device first.
+        ``results`` (from make_result_buffers) receives reward / reward64 / done / stats instead of the
+        env's own tensors.
         Returns (obs float32 CUDA, reward float32 [E] CUDA, done uint8 [E] CUDA)."""
         import torch
         obs = self.obs if out is None else out
+        rew = self.reward if results is None else results["reward"]
+        rew64 = self.reward64 if results is None else results["reward64"]
+        dn = self.done if results is None else results["done"]
+        stats = self.stats if results is None else results["stats"]
         act = actions
         if not torch.is_tensor(act):
             act = torch.as_tensor(np.asarray(act))
@@ -150,12 +166,11 @@ class _VecEnv:
         act = act.contiguous()
         with torch.cuda.device(self.device):
             _lib.check(self._lib.mcov_step(self._handle, act.data_ptr(), fmt, obs.data_ptr(),
-                                           self.reward.data_ptr(), self.reward64.data_ptr(),
-                                           self.done.data_ptr(),
-                                           self.stats.data_ptr() if want_stats else None,
+                                           rew.data_ptr(), rew64.data_ptr(), dn.data_ptr(),
+                                           stats.data_ptr() if want_stats else None,
                                            self._stream()))
         self._keep_act = act
-        return obs, self.reward, self.done
+        return obs, rew, dn
 
     def observe(self, out=None):
         import torch
