@@ -126,6 +126,20 @@ __device__ __forceinline__ void prefetch_l1(const void* ptr) {
 __device__ __forceinline__ void prefetch_l2(const void* ptr) {
     asm volatile("prefetch.global.L2 [%0];" :: "l"(ptr));
 }
+#ifndef MCOV_ST_MODE
+#define MCOV_ST_MODE 0                       // observation store policy: 0 .cs  1 default  2 .cg  3 .wt
+#endif
+__device__ __forceinline__ void obs_store(float4* ptr, const float4 v) {
+#if MCOV_ST_MODE == 0
+    __stcs(ptr, v);
+#elif MCOV_ST_MODE == 1
+    *ptr = v;
+#elif MCOV_ST_MODE == 2
+    __stcg(ptr, v);
+#else
+    __stwt(ptr, v);
+#endif
+}
 #ifndef MCOV_PF_NEXT
 #define MCOV_PF_NEXT 0                       // measured on B200 (C5): 0.213 -> 0.233 ms with it on — the step is DRAM-throughput bound, extra line fetches cost more than the latency they hide
 #endif
@@ -196,8 +210,10 @@ __device__ __forceinline__ void prefetch_next_env(const DecParams& p, const Pref
     }
 }
 
+enum { PASS_DONE = 0, PASS_AGAIN = 2 };   // env_pass results
+
 template <class SP>
-__device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut,
+__device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut,
                                          const int e, const int mode, const Prefetch& cur,
                                          const Grp<SP::G>& g, const Prefetch& nxt, const int e_next) {
     constexpr int G = SP::G;
@@ -329,7 +345,7 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
     }
     if (mode == MODE_STEP && !(p.phases & PH_SENSE)) {
         if (lg == 0) p.move_scratch[e] = make_uint2((uint32_t)ncoll, shown);
-        return false;
+        return PASS_DONE;
     }
     g.sync();
 
@@ -624,30 +640,30 @@ __device__ __forceinline__ bool env_pass(const DecParams& p, const GroupSmem& sm
         head->ep_return = 0.0;
         p.needs_reset[e] = 0;
     }
-    if (again) return true;                                        // obs comes from the reset pass
+    if (again) return PASS_AGAIN;                                  // obs comes from the reset pass
 
     // ---- observation block: bit stream -> float32, coalesced 128-bit streaming stores ----------
     float* obs_e = p.obs + (size_t)e * p.obs_env_floats;
 #if MCOV_PF_NEXT
     if (e_next >= 0) prefetch_next_env<SP>(p, nxt, e_next, g);
 #endif
-    if (p.debug & 1) return false;                                 // MCOV_DEBUG=1: profiling aid, no obs store
+    if (p.debug & 1) return PASS_DONE;                             // MCOV_DEBUG=1: profiling aid, no obs store
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
         const int nf4 = p.obs_env_floats >> 2;
-        // float4 q = lg + G*t holds bits [4q, 4q+4): word t*(G/8) + (lg>>3), nibble lg&7
-        const uint32_t* bw = sm.bits + (lg >> 3);
-        const int nib = (lg & 7) * 4;
+        // float4 q = lg + G*t holds bits [4q, 4q+4): word q>>3, nibble q&7
         float4* d = dst + lg;
         const int iters = (nf4 - lg + G - 1) / G;
 #pragma unroll 4
-        for (int t = 0; t < iters; ++t)
-            __stcs(d + t * G, lut[(bw[t * (G / 8)] >> nib) & 15u]);
+        for (int t = 0; t < iters; ++t) {
+            const int q = lg + t * G;
+            obs_store(d + t * G, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
+        }
     } else {
         for (int k = lg; k < p.obs_env_floats; k += G)
             __stcs(obs_e + k, ((sm.bits[k >> 5] >> (k & 31)) & 1u) ? 1.0f : 0.0f);
     }
-    return false;
+    return PASS_DONE;
 }
 
 template <class SP>
@@ -667,7 +683,7 @@ dec_env_kernel(const DecParams p) {
         lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
                              (t & 8u) ? 1.0f : 0.0f);
     }
-    if (g.lg < MCOV_STATS_LEN) sm.stats[g.lg] = 0.0;
+    for (int k = g.lg; k < MCOV_STATS_LEN; k += G) sm.stats[k] = 0.0;
     __syncthreads();
 
     const int gg = blockIdx.x * gpc + gi, gtot = gridDim.x * gpc;
@@ -685,8 +701,18 @@ dec_env_kernel(const DecParams p) {
             else if (p.mask_from_flags) act = p.needs_reset[e];
             if (!act) continue;                                    // group-uniform
         }
+        if (p.debug & 2) {                                         // MCOV_DEBUG=2: profiling aid, obs store only
+            float4* d = reinterpret_cast<float4*>(p.obs + (size_t)e * p.obs_env_floats) + g.lg;
+            const int iters = ((p.obs_env_floats >> 2) - g.lg + G - 1) / G;
+#pragma unroll 4
+            for (int t = 0; t < iters; ++t) {
+                const int q = g.lg + t * G;
+                obs_store(d + t * G, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
+            }
+            continue;
+        }
         const int e_next = (mode == MODE_STEP && e + gtot < p.E) ? e + gtot : -1;
-        while (env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next)) m = MODE_RESET;   // fused auto-reset
+        while (env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
     }
 
     // ---- episode statistics: group sums -> CTA row -> last CTA folds all rows (single launch) --
@@ -820,7 +846,7 @@ inline int pick_group(const mcov_config& c, int num_sms) {
     // MCOV_DEC_GROUP=8|16|32 pins the width (tests run every width on the same traces; tuning)
     if (const char* f = getenv("MCOV_DEC_GROUP")) {
         const int v = atoi(f);
-        if ((v == 8 || v == 16 || v == 32) && v >= c.num_robots) g = v;
+        if ((v == 4 || v == 8 || v == 16 || v == 32) && v >= c.num_robots) g = v;
     }
     return g;
 }
@@ -900,7 +926,9 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     const bool c2 = plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5;
     const bool c3 = plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5;
     const bool c4 = plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5;
-    if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(s, p, st);
+    if (c2 && s.G == 4) err = launch_dec_t<Spec<4, false, 4, 2, 5>>(s, p, st);
+    else if (s.G == 4) err = lidar ? launch_dec_t<Spec<4, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<4, false, 0, 0, 0>>(s, p, st);
+    else if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(s, p, st);
     else if (c2 && s.G == 16) err = launch_dec_t<Spec<16, false, 4, 2, 5>>(s, p, st);
     else if (c2 && s.G == 32) err = launch_dec_t<Spec<32, false, 4, 2, 5>>(s, p, st);
     else if (c3 && s.G == 8) err = launch_dec_t<Spec<8, true, 8, 10, 5>>(s, p, st);

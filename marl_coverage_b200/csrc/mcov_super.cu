@@ -180,7 +180,10 @@ __device__ void write_state(const SuperParams& p, const SuperSmem& sm, const Env
 // The six planes that do not depend on the distance transform (positions, observed obstacles, free)
 // are cut into warp items of IT float4; warps claim items from a shared counter, so the warps that
 // run the transform simply join the writers when they are done.
-constexpr int IT = 128;                                      // float4 per warp item (4 per lane)
+#ifndef MCOV_SUPER_IT
+#define MCOV_SUPER_IT 160
+#endif
+constexpr int IT = MCOV_SUPER_IT;                            // float4 per warp item (IT / 32 per lane)
 
 __device__ void write_fixed_planes(const SuperParams& p, SuperSmem& sm, const EnvSlot& slot, int e, int lane) {
     const int N = p.N, W = p.g.W, L = p.g.L, Wp = p.g.Wp;
@@ -207,14 +210,15 @@ __device__ void write_fixed_planes(const SuperParams& p, SuperSmem& sm, const En
                 const int q = base + lane + 32 * t;
                 if (q < nz) __stcs(dst + q, z4);
             }
-            // the lane that zero-filled a robot's float4 patches the 1.0 (same thread: program order)
-            for (int j = 0; j < N; ++j) {
-                const uint32_t pv = slot.pos[j];
+            // lane j patches robot j's 1.0 into the float4 another lane just zero-filled: __syncwarp orders
+            // the two stores (one cell per robot, N <= 32)
+            __syncwarp();
+            if (lane < N) {
+                const uint32_t pv = slot.pos[lane];
                 const int cell = unpack_x(pv) * L + unpack_y(pv);
-                const int plane = p.use_scanning ? 0 : j;
+                const int plane = p.use_scanning ? 0 : lane;
                 const int q = plane * qp + (cell >> 2);
-                if (q >= base && q < base + IT && ((q - base) & 31) == lane)
-                    obs_e[(size_t)plane * WL + cell] = 1.0f;
+                if (q >= base && q < base + IT) obs_e[(size_t)plane * WL + cell] = 1.0f;
             }
         } else {
             const int base = (it - n1) * IT;

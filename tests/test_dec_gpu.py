@@ -34,11 +34,11 @@ def test_dec_golden_batched_copies(name):
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=67, check_envs=(0, 31, 66))
 
 
-@pytest.mark.parametrize("group", [8, 16, 32])
+@pytest.mark.parametrize("group", [4, 8, 16, 32])
 @pytest.mark.parametrize("name", ["dec_c2_square_100", "dec_lidar_21x10_100", "dec_mapsharing_comm12",
                                   "dec_square_thresh_incr", "dec_single_square_tool"])
 def test_dec_golden_every_group_width(name, group, monkeypatch):
-    """The kernel picks 8/16/32 lanes per env from the batch size; every width must give the same
+    """The kernel picks 4/8/16/32 lanes per env from the batch size; every width must give the same
     bits (MCOV_DEC_GROUP pins it)."""
     from marl_coverage_b200 import VecDecGridRL
     from gpu_helpers import replay_trace_on_gpu
@@ -56,3 +56,4 @@ def test_dec_lidar_float64_march_path(name, monkeypatch):
     monkeypatch.setenv("MCOV_LIDAR_FP64", "1")
     tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=3, check_envs=(0, 2))
+
