@@ -526,8 +526,51 @@ def run_c2_extra(torch, device):
     ms, per, _ = timed_steps(torch, None, env, acts, 5, 100, 1, flush=flush)
     per.sort()
     med = per[len(per) // 2]
-    return {"workload": desc, "value": E * cfg["numrobot"] / (med * 1e-3), "unit": UNIT,
-            "ms_per_step_median": med, "l2": "flushed between timed steps"}
+    out = {"workload": desc, "value": E * cfg["numrobot"] / (med * 1e-3), "unit": UNIT,
+           "ms_per_step_median": med, "l2": "flushed between timed steps"}
+    try:
+        out["cuda_graph"] = run_c2_graph(torch, device, kind, grid_name, E, cfg, n_maps)
+    except Exception as ex:                                  # the extra must never cost the bench line
+        out["cuda_graph"] = {"error": repr(ex)[:200]}
+    return out
+
+
+def run_c2_graph(torch, device, kind, grid_name, E, cfg, n_maps, replicas=6, rounds=10, replays=5):
+    """Same 4096-env step, launch overhead taken out: `replicas` independent env batches stepped round-robin
+    inside one CUDA graph (the C ABI only enqueues on the caller's stream, so a rollout captures as is).
+    The batches' working sets (6 x 85 MB) exceed the 126 MB L2 several times over, so every step finds its
+    state cold without an explicit flush."""
+    N = cfg["numrobot"]
+    envs = []
+    for r in range(replicas):
+        env, _ = make_env(kind, grid_name, cfg, E, device, r * E)
+        env.reset(map_idx=(torch.arange(E, device=device, dtype=torch.int32) + r) % n_maps)
+        envs.append(env)
+    acts = gen_actions(torch, device, rounds, replicas * E, N, 321).view(rounds, replicas, E, N)
+    side = torch.cuda.Stream(device)
+    side.wait_stream(torch.cuda.current_stream(device))
+    with torch.cuda.stream(side):
+        for r, env in enumerate(envs):
+            env.step(acts[0, r], want_stats=True)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for k in range(rounds):
+                for r, env in enumerate(envs):
+                    env.step(acts[k, r], want_stats=True)
+        g.replay()
+        side.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(side)
+        for _ in range(replays):
+            g.replay()
+        e1.record(side)
+        side.synchronize()
+    torch.cuda.current_stream(device).wait_stream(side)
+    steps = replays * rounds * replicas
+    ms = e0.elapsed_time(e1) / steps
+    ws = sum(e._arena.numel() + e.obs.numel() * 4 for e in envs)
+    return {"value": E * N / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": steps,
+            "l2": "%d env batches round-robin, working set %.0f MB > 126 MB L2, no flush" % (replicas, ws / 1e6)}
 
 
 def load_traffic(workload):

@@ -12,7 +12,8 @@
  *   - plain C types only; every pointer suffixed _dev is DEVICE memory owned by the caller
  *     (PyTorch allocates it), every pointer suffixed _host is host memory;
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued asynchronously on it,
- *     nothing synchronises, everything is CUDA-graph capturable;
+ *     nothing synchronises, everything is CUDA-graph capturable (tests/test_graph_gpu.py; scalar arguments
+ *     such as the reset seed are frozen into a captured graph like any kernel parameter);
  *   - every function returns MCOV_OK (0) or a negative mcov_status; the message is available from
  *     mcov_last_error() (thread local).  Nothing throws, nothing calls exit();
  *   - the library owns only the opaque handle.  Simulator state lives in a caller-owned arena

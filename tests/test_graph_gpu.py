@@ -1,0 +1,75 @@
+"""The C ABI promises that every call only enqueues work on the caller's stream (include/mcov.h): a rollout
+of several steps must therefore be capturable in a CUDA graph and replay to the same bits as eager stepping."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+DEC = dict(numrobot=4, maxsteps=30, collision_penalty=5, done_thresh=0.6, done_incr=0, terminal_reward=30,
+           dist_reward=0, train_maxsteps=30, test_maxsteps=30, egoradius=5, mini_map_rad=0, comm_radius=0,
+           allow_comm=0, map_sharing=0, single_square_tool=0, dijkstra_input=0, sensor_type="square_sensor",
+           sensor_config={"range": 2})
+SUPER = dict(numrobot=3, train_maxsteps=30, test_maxsteps=30, collision_penalty=5, senseradius=2, free_penalty=0.2,
+             done_thresh=0.5, done_incr=0, terminal_reward=30, dist_reward=0, use_scanning=0)
+
+
+@pytest.mark.parametrize("kind", ["dec", "dec_lidar", "super"])
+def test_rollout_in_a_cuda_graph_equals_eager(kind):
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, load_grid_set
+    grids = load_grid_set("bg2_100x100", 5)
+    cfg = dict(SUPER) if kind == "super" else dict(DEC)
+    if kind == "dec_lidar":
+        cfg.update(sensor_type="lidar", sensor_config={"range": 6, "num_lasers": 15})
+    cls = VecSuperGridRL if kind == "super" else VecDecGridRL
+    E, N, T = 301, cfg["numrobot"], 12
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(3)
+    acts = torch.randint(0, 4, (3 * T, E, N), dtype=torch.uint8, device="cuda", generator=gen)
+
+    def make():
+        env = cls(grids, cfg, num_envs=E, auto_reset=True, truncate_steps=30, seed=9)
+        env.reset(seed=1234)
+        return env
+
+    eager, graphed = make(), make()
+    obs_log = torch.empty((T,) + tuple(graphed.obs_shape), device="cuda")
+    rew_log = torch.empty((T, E), dtype=torch.float64, device="cuda")
+    done_log = torch.empty((T, E), dtype=torch.uint8, device="cuda")
+    stats_log = torch.empty((T, 8), dtype=torch.float64, device="cuda")
+    cursor = torch.zeros((), dtype=torch.int64, device="cuda")      # which block of T action rows to play
+    act_buf = torch.empty((T, E, N), dtype=torch.uint8, device="cuda")
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        graphed.step(acts[0], want_stats=True)                       # warm-up launch outside the capture
+        graphed.reset(seed=1234)                                      # kernel parameters (the auto-reset seed
+        g = torch.cuda.CUDAGraph()                                    # among them) are frozen into the graph
+        with torch.cuda.graph(g, stream=side):
+            for t in range(T):
+                o, r, d = graphed.step(act_buf[t], want_stats=True)
+                obs_log[t].copy_(o)
+                rew_log[t].copy_(graphed.reward64)
+                done_log[t].copy_(d)
+                stats_log[t].copy_(graphed.stats)
+    torch.cuda.current_stream().wait_stream(side)
+    graphed.reset(seed=1234)
+    # the device RNG is keyed by (seed of the reset call, env id, episode counter): give `eager` the same history
+    eager.step(acts[0], want_stats=True)
+    eager.reset(seed=1234)
+    eager.reset(seed=1234)
+    assert torch.equal(graphed.obs, eager.obs)
+    episodes = 0.0
+    for block in range(3):
+        act_buf.copy_(acts[block * T:(block + 1) * T])
+        g.replay()
+        torch.cuda.synchronize()
+        for t in range(T):
+            o, r, d = eager.step(acts[block * T + t], want_stats=True)
+            assert torch.equal(obs_log[t], o), (kind, block, t)
+            assert torch.equal(rew_log[t], eager.reward64)
+            assert torch.equal(done_log[t], d)
+            assert torch.equal(stats_log[t], eager.stats)
+            episodes += float(eager.stats[0].item())
+    assert episodes > 0, "the rollout must cross auto-resets inside the graph"
