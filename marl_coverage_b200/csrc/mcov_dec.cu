@@ -41,7 +41,10 @@ constexpr int MAX_WARPS = 8;
 #endif
 
 // floor(k / d) for k < 2^26, d <= 64, magic = ceil(2^32 / d)
-__device__ __forceinline__ int fast_div(int k, uint32_t magic) { return (int)__umulhi((uint32_t)k, magic); }
+// (d == 1 gives magic = 2^32 = 0 in 32 bits: the quotient is k itself)
+__device__ __forceinline__ int fast_div(int k, uint32_t magic) {
+    return magic ? (int)__umulhi((uint32_t)k, magic) : k;
+}
 
 // Draws map + start poses on the device (see draw_starts in mcov_common.cuh).
 __device__ void draw_reset(const DecParams& p, int e, uint32_t episode, uint32_t* posS, int* map_out) {

@@ -45,7 +45,7 @@ def _super_cfg(rng, N):
                 use_scanning=int(rng.random() < 0.4))
 
 
-def _run_case(kind, seed, E=9, T=40):
+def _run_case(kind, seed, E=9, T=40, force=None):
     import torch
     from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL
     rng = np.random.default_rng(seed)
@@ -53,8 +53,11 @@ def _run_case(kind, seed, E=9, T=40):
     if seed % 3 == 0:
         L = (L // 4) * 4 + 4                 # exercise the vectorised store path too
     N = int(rng.integers(1, 9 if kind == "dec" else 17))
+    force = dict(force or {})
+    W, L, N = force.pop("W", W), force.pop("L", L), force.pop("N", N)
     grids = [_rand_map(rng, W, L, float(rng.choice([0.0, 0.1, 0.3]))) for _ in range(3)]
     cfg = _dec_cfg(rng, N) if kind == "dec" else _super_cfg(rng, N)
+    cfg.update(force)
     np.random.seed(seed)
     mk = (lambda: oc.OracleDecGridRL(grids, cfg, use_graph=True)) if kind == "dec" else \
          (lambda: oc.OracleSuperGridRL(grids, cfg))
@@ -127,3 +130,47 @@ def test_dec_random_vs_oracle(seed):
 @pytest.mark.parametrize("seed", range(24))
 def test_super_random_vs_oracle(seed):
     _run_case("super", 2000 + seed)
+
+
+# ---- limits of the ABI (include/mcov.h: MCOV_MAX_ROBOTS 32, MCOV_MAX_RADIUS 15, odd num_lasers) and degenerate shapes
+EDGE = [
+    ("dec", dict(N=32, W=40, L=33, egoradius=2, sensor_type="square_sensor", sensor_config={"range": 1},
+                 mini_map_rad=0, dijkstra_input=0, dist_reward=0)),
+    ("dec", dict(N=17, W=35, L=70, egoradius=3, sensor_type="lidar", sensor_config={"range": 4, "num_lasers": 9},
+                 mini_map_rad=0)),
+    ("dec", dict(N=2, W=50, L=50, egoradius=15, sensor_type="square_sensor", sensor_config={"range": 15},
+                 mini_map_rad=0)),
+    ("dec", dict(N=3, W=40, L=40, egoradius=4, sensor_type="lidar", sensor_config={"range": 15, "num_lasers": 1},
+                 mini_map_rad=0)),
+    ("dec", dict(N=2, W=30, L=30, egoradius=5, sensor_type="lidar", sensor_config={"range": 6, "num_lasers": 1023},
+                 mini_map_rad=0)),
+    ("dec", dict(N=1, W=5, L=6, egoradius=1, sensor_type="square_sensor", sensor_config={"range": 0},
+                 mini_map_rad=0)),
+    ("dec", dict(N=4, W=33, L=31, egoradius=7, mini_map_rad=15, sensor_type="square_sensor",
+                 sensor_config={"range": 3})),
+    ("super", dict(N=31, W=30, L=36, senseradius=1)),
+    ("super", dict(N=2, W=5, L=4, senseradius=4)),
+    ("super", dict(N=3, W=64, L=32, senseradius=15)),
+    ("super", dict(N=1, W=7, L=129, senseradius=0, use_scanning=1)),
+]
+
+
+@pytest.mark.parametrize("case", range(len(EDGE)))
+def test_limits_and_degenerate_shapes_vs_oracle(case):
+    kind, force = EDGE[case]
+    _run_case(kind, 7000 + case, E=3, T=25, force=force)
+
+
+def test_bad_configs_are_refused():
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, _lib
+    g = [np.ones((10, 10))]
+    base = _dec_cfg(np.random.default_rng(0), 2)
+    base.update(sensor_type="square_sensor", sensor_config={"range": 2}, egoradius=3, mini_map_rad=0)
+    for bad in (dict(numrobot=33), dict(egoradius=16), dict(sensor_config={"range": 16}),
+                dict(sensor_type="lidar", sensor_config={"range": 3, "num_lasers": 8})):
+        with pytest.raises((_lib.McovError, AssertionError, ValueError)):
+            VecDecGridRL(g, dict(base, **bad), num_envs=2)
+    with pytest.raises(_lib.McovError):
+        VecSuperGridRL(g, dict(_super_cfg(np.random.default_rng(0), 2), senseradius=16), num_envs=2)
+    with pytest.raises((ValueError, _lib.McovError)):
+        VecDecGridRL([np.full((10, 10), 2.0)], base, num_envs=2)      # cell values other than -1 / 0 / +1
