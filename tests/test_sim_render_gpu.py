@@ -139,3 +139,40 @@ def test_compat_render_types():
     assert f.dtype == np.float64 and f.shape == g["frame_super_rect"].shape
     assert np.array_equal(f, oc.render_frame(sup._observed_obstacles, sup._free < 1,
                                              sup.get_pos_image()[0], 1075, False).astype(np.float64))
+
+
+@pytest.mark.parametrize("kind", ["dec", "super"])
+def test_render_large_map_scale_one(kind):
+    """1073 x 1073 maps: scale factor 1, DecGridRL's bordered 1075 fills the canvas exactly (no border rows)."""
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, load_grid_set
+    grids = load_grid_set("bg2_1073x1073", 1)
+    N = 5
+    if kind == "dec":
+        cfg = dict(numrobot=N, maxsteps=100, collision_penalty=5, done_thresh=1, done_incr=0, terminal_reward=30,
+                   dist_reward=0, train_maxsteps=100, test_maxsteps=100, egoradius=5, mini_map_rad=0, comm_radius=0,
+                   allow_comm=0, map_sharing=0, single_square_tool=0, dijkstra_input=0, sensor_type="lidar",
+                   sensor_config={"range": 9, "num_lasers": 21})
+        vec, orc = VecDecGridRL(grids, cfg, num_envs=2, seed=4), oc.OracleDecGridRL(grids, cfg)
+    else:
+        cfg = dict(numrobot=N, train_maxsteps=100, test_maxsteps=100, collision_penalty=5, senseradius=3,
+                   free_penalty=0.2, done_thresh=1, done_incr=0, terminal_reward=30, dist_reward=0, use_scanning=1)
+        vec, orc = VecSuperGridRL(grids, cfg, num_envs=2, seed=4), oc.OracleSuperGridRL(grids, cfg)
+    vec.reset(map_idx=np.zeros(2, np.int32))
+    start = vec.positions()[1].cpu().numpy()
+    np.random.seed(0)
+    orc.reset(False, None, start_xy=start, map_index=0)
+    rng = np.random.RandomState(8)
+    for _ in range(15):
+        a = rng.randint(0, 4, size=(2, N)).astype(np.uint8)
+        vec.step(torch.from_numpy(a))
+        orc.step(a[1].astype(np.int64))
+    frame = vec.render(env_ids=[1]).cpu().numpy()[0]
+    robots = np.zeros((orc._gridwidth, orc._gridlen))
+    robots[orc._xinds, orc._yinds] = 1
+    if kind == "dec":
+        want = oc.render_frame(orc._observed_obstacles, orc._visited, robots, 1024, True)
+    else:
+        want = oc.render_frame(orc._observed_obstacles, orc._covered, robots, 1075, False)
+    assert frame.shape == want.shape == (1075, 1075, 3) if kind == "dec" else frame.shape == want.shape
+    assert np.array_equal(frame, want)
