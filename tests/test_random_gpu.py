@@ -45,6 +45,26 @@ def _super_cfg(rng, N):
                 use_scanning=int(rng.random() < 0.4))
 
 
+def _wide(rng, kind):
+    """Forced values drawn over the whole range include/mcov.h accepts (soak runs: MCOV_SOAK=n)."""
+    f = dict(W=int(rng.integers(3, 70)), L=int(rng.integers(3, 70)), N=int(rng.integers(1, 33)))
+    while f["W"] * f["L"] < 3 * f["N"] + 20:
+        f["W"] += 3
+        f["L"] += 2
+    if kind == "dec":
+        f["egoradius"] = int(rng.integers(0, 16))
+        f["mini_map_rad"] = int(rng.integers(1, 16)) if rng.random() < 0.2 else 0
+        f["comm_radius"] = int(rng.integers(0, 40))
+        if rng.random() < 0.5:
+            f.update(sensor_type="lidar", sensor_config={"range": int(rng.integers(0, 16)),
+                                                         "num_lasers": int(rng.choice([1, 3, 7, 21, 45, 201]))})
+        else:
+            f.update(sensor_type="square_sensor", sensor_config={"range": int(rng.integers(0, 16))})
+    else:
+        f["senseradius"] = int(rng.integers(0, 16))
+    return f
+
+
 def _run_case(kind, seed, E=9, T=40, force=None):
     import torch
     from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL
@@ -153,6 +173,13 @@ EDGE = [
     ("super", dict(N=3, W=64, L=32, senseradius=15)),
     ("super", dict(N=1, W=7, L=129, senseradius=0, use_scanning=1)),
 ]
+
+
+@pytest.mark.parametrize("k", range(int(__import__("os").environ.get("MCOV_SOAK", "6"))))
+@pytest.mark.parametrize("kind", ["dec", "super"])
+def test_whole_parameter_range_vs_oracle(kind, k):
+    seed = 9000 + k
+    _run_case(kind, seed, E=4, T=20, force=_wide(np.random.default_rng(seed), kind))
 
 
 @pytest.mark.parametrize("case", range(len(EDGE)))
