@@ -398,7 +398,9 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 const uint32_t pi = sm.posF[i];
                 const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
                 sm.wallW[idx] = (x >= 0 && x < W) ? read_window(wall_g + map_off, Wp, strips, x, y0, S) : 0xffffffffu;
-                sm.winF[idx] = 0;
+                // table walk: every beam starts on the robot's own (walkable) cell, lidar.py:30 — set it here
+                // once instead of by n_lasers colliding shared-memory atomics
+                sm.winF[idx] = (p.lidar_cells && r == R) ? (1u << R) : 0u;
                 sm.winO[idx] = 0;
             }
             g.sync();
@@ -407,7 +409,9 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 // walk the <= 16 window cells of the beam until the first wall
                 const int nl = p.n_lasers;
                 for (int idx = lg; idx < N * nl; idx += G) {
-                    const int i = fast_div(idx, p.l_magic), l = idx - i * nl;
+                    // neighbouring lanes take the same beam of different robots: beams of one robot share
+                    // cells near the origin and would collide on the same shared-memory words
+                    const int l = div_n(idx), i = idx - l * N;
                     const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
                     const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
                     const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
@@ -415,7 +419,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     uint32_t* wf = sm.winF + i * S;
                     uint32_t* wo = sm.winO + i * S;
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) {
+                    for (int k = 1; k < 16; ++k) {
                         const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
                         if (cell == 0xffffu) break;
                         const int rx = (int)(cell & 0xffu), ry = (int)(cell >> 8);
