@@ -223,6 +223,10 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     constexpr bool LIDAR = SP::LIDAR;
     const int N = SP::FIXED ? SP::CN : p.N, R = SP::FIXED ? SP::CR : p.R, ego = SP::FIXED ? SP::CE : p.ego;
     const int C = SP::FIXED ? 3 : p.C;
+    // the compile-time shapes are only dispatched with these options off (launch_dec), so they fold away
+    const bool single_tool = !SP::FIXED && p.single_tool;
+    const int comm_radius = SP::FIXED ? 0 : p.comm_radius;
+    const int phases = SP::FIXED ? (PH_MOVE | PH_SENSE) : p.phases;          // split only for dist_reward (C == 4)
     const int S = 2 * R + 1, ow = 2 * ego + 1, rad = ego > R ? ego : R, RW = 2 * rad + 1;
     const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
     const int lg = g.lg;
@@ -295,7 +299,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
         } else {
             u = (int)(cur.act8 & 3u);
         }
-        if (!sentinel && (p.phases & PH_MOVE)) {
+        if (!sentinel && (phases & PH_MOVE)) {
             // ---- sequential, collision-checked moves (dec_grid_rl.py:128-145,171-204) --------
             // Dec table: 0:x+1  1:y+1  2:x-1  3:y-1
             const int tx = px + (u == 0) - (u == 2);
@@ -335,18 +339,18 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     for (int k = lg; k < p.bits_words; k += G) sm.bits[k] = 0;
 
     // ---- communication graph (dec_grid_rl.py:374-391): Chebyshev ball, diagonal included ------
-    if (mode != MODE_OBSERVE && (p.comm_radius > 0 || fresh)) {
+    if (mode != MODE_OBSERVE && (comm_radius > 0 || fresh)) {
         uint32_t myadj = 1u << lg;
-        if (p.comm_radius > 0) {
+        if (comm_radius > 0) {
             for (int i = 0; i < N; ++i) {
                 const int xi = g.shfl(px, i), yi = g.shfl(py, i);
-                const uint32_t b = g.ballot((lg < N) && max(abs(px - xi), abs(py - yi)) <= p.comm_radius);
+                const uint32_t b = g.ballot((lg < N) && max(abs(px - xi), abs(py - yi)) <= comm_radius);
                 if (lg == i) myadj = b;
             }
         }
         if (lg < N) reinterpret_cast<uint32_t*>(hrec + p.off_adj)[lg] = myadj;
     }
-    if (mode == MODE_STEP && !(p.phases & PH_SENSE)) {
+    if (mode == MODE_STEP && !(phases & PH_SENSE)) {
         if (lg == 0) p.move_scratch[e] = make_uint2((uint32_t)ncoll, shown);
         return PASS_DONE;
     }
@@ -456,7 +460,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 }
             }
             }
-            if (p.single_tool) {
+            if (single_tool) {
                 g.sync();
                 for (int idx = lg; idx < N * S; idx += G) {
                     const int i = div_s(idx), r = idx - i * S;
@@ -507,7 +511,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             const uint32_t m0 = (uint32_t)m64, m1 = (uint32_t)(m64 >> 32);
             if (q0) { o0 = __ldg(&wall_g[map_off + w0]) & m0; f0 = __ldg(&tpos_g[map_off + w0]) & m0; }
             if (q1) { o1 = __ldg(&wall_g[map_off + w0 + Wp]) & m1; f1 = __ldg(&tpos_g[map_off + w0 + Wp]) & m1; }
-            if (p.single_tool) {                                   // dec_grid_rl.py:233-234
+            if (single_tool) {                                     // dec_grid_rl.py:233-234
                 const uint64_t c64 = (a2 == rad) ? (1ull << (sh + rad)) : 0ull;
                 f0 = q0 ? (uint32_t)c64 : 0u;
                 f1 = q1 ? (uint32_t)(c64 >> 32) : 0u;
@@ -546,7 +550,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                         uint32_t jl, jh;
                         split_words(sm.winF[j * S + (x - xj + R)], y0j, jl, jh);
                         add = (sk == s0j) ? jl : jh;
-                    } else if (p.single_tool) {
+                    } else if (single_tool) {
                         add = (x == xj && (yj >> 5) == sk) ? (1u << (yj & 31)) : 0u;
                     } else {
                         add = __ldg(&tpos_g[map_off + w0 + k * Wp]) & ymask_in_strip(yj, R, S, sk);
@@ -607,7 +611,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             } else {
                 for (int k = 0; k < ncoll; ++k) r -= p.cp;         // dec_grid_rl.py:185-204
                 double obs_r = (double)cnt;
-                if (p.dist_term) obs_r = (double)p.dist_term[e] + (double)cnt;   // row D11
+                if (!SP::FIXED && p.dist_term) obs_r = (double)p.dist_term[e] + (double)cnt;   // row D11
                 r += obs_r;
                 const int cs = cs0 + 1;                            // :154
                 // percent_covered sums over robots (quirk A.3.3); min(thresh, 1) <= pct  (:156-157)
@@ -928,7 +932,7 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.debug = debug;
     if ((uint64_t)p.E * p.N * p.g.PW >= 0xffffffffull) return cudaErrorInvalidValue;   // 32-bit word offsets
     cudaError_t err;
-    const bool plain = p.C == 3;
+    const bool plain = p.C == 3 && !p.single_tool && p.comm_radius == 0;
     // instantiations for the BASELINE configs (C2/C5, C3, C4), generic otherwise
     const bool c2 = plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5;
     const bool c3 = plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5;
