@@ -27,6 +27,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+STATS_BLOCK = 8        # steps per statistics all-reduce at N > 1 (every step's vector is reduced, 8 per call)
 METRIC = "agent-steps/sec (batched env step, 1/2/4/8 B200) and % of HBM roofline"
 UNIT = "agent-steps/s"
 
@@ -246,7 +247,8 @@ def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, f
     With `flush` (a big tensor) the L2 is overwritten between steps and each step is timed alone."""
     from marl_coverage_b200.sharding import StatsReducer
     dev = env.device
-    red = StatsReducer(dev, world=world)                 # NCCL SUM of the 64-byte statistics vector
+    # NCCL SUM of every step's 64-byte statistics vector, STATS_BLOCK steps per collective on a side stream
+    red = StatsReducer(dev, world=world, block=STATS_BLOCK if world > 1 else 1)
     main = torch.cuda.current_stream(dev)
 
     def one(k):
@@ -267,6 +269,7 @@ def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, f
         for k in range(warmup, warmup + steps):
             one(k)
         if world > 1:
+            red.flush()                                  # the timed steps' statistics are reduced inside the region
             main.wait_stream(red.side)
         e1.record(main)
         torch.cuda.synchronize(dev)
@@ -335,11 +338,34 @@ def run_gpu(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
+
+    # a second env batch of the same shape carries the load around the timed steps, so the measured batch
+    # keeps its episode phase (all envs truncate together at multiples of train_maxsteps: a time-based soak
+    # on the measured batch would move that mass-reset step in or out of the timed region at random)
+    env_soak, _ = make_env(kind, grid_name, cfg, E, device, env_id_base=rank * E)
+    env_soak.reset(map_idx=map_idx)
+
+    def soak(seconds):
+        """Untimed stepping load so that the 100 ms clock sampler sees the GPU in the state the timed steps
+        run in (the timed region itself can be shorter than one sampling period)."""
+        t_end = time.perf_counter() + seconds
+        k = 0
+        while time.perf_counter() < t_end:
+            for _ in range(50):
+                env_soak.step(acts[k % T])
+                k += 1
+            torch.cuda.synchronize(device)
+
+    soak(0.6)
     launches0 = env.launch_count
     ms, per, total_stats = timed_steps(torch, dist, env, acts, Wm, K, world, flush=flush)
     launches = env.launch_count - launches0
     launches_timed = int(round(launches * K / float(K + Wm)))
+    soak(0.4)
     clk = clocks.stop() if rank == 0 else None
+    del env_soak
+    if clk is not None:
+        clk["window"] = "timed steps bracketed by 0.6 s + 0.4 s of the same stepping load (100 ms sampling period)"
 
     t = torch.tensor([ms], dtype=torch.float64, device=device)
     if world > 1:
@@ -490,7 +516,8 @@ def run_gpu(args):
                        "obs_shape": list(env.obs_shape), "auto_reset": True, "truncate_steps": cfg["train_maxsteps"],
                        "l2": ("flushed between timed steps (256 MiB write)" if flush is not None else
                               "working set %.2f GB per GPU >> 126 MB L2, no flush" % (ws_bytes / 1e9)),
-                       "stats_allreduce": "NCCL per step on a side stream" if world > 1 else "none (1 GPU)"},
+                       "stats_allreduce": ("NCCL SUM of every step's statistics vector on a side stream, %d steps per "
+                                           "collective" % STATS_BLOCK) if world > 1 else "none (1 GPU)"},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": launches_timed, "clocks": clk,
             "episode_stats": {"episodes": st[0], "mean_return": (st[1] / st[0]) if st[0] else None,

@@ -327,6 +327,14 @@ int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_d
         return fail(MCOV_ERR_BAD_CONFIG, "n_maps/W/L %d/%d/%d", n_maps, W, L);
     if (!aligned(wall_dev, 16) || !aligned(pos_dev, 16))
         return fail(MCOV_ERR_ALIGN, "map planes must be 16-byte aligned");
+    {
+        const mcov::Geometry gq = mcov::make_geometry(W, L);
+        const unsigned long long words = (unsigned long long)env->cfg.num_envs * env->cfg.num_robots * gq.PW;
+        if (env->cfg.env_type == MCOV_ENV_DEC && words >= 0xffffffffull)
+            return fail(MCOV_ERR_BAD_CONFIG, "num_envs x numrobot x plane words = %llu exceeds the kernel's 32-bit "
+                        "plane offsets: shard the batch over more handles (<= %llu envs of this map size each)",
+                        words, 0xfffffffeull / ((unsigned long long)env->cfg.num_robots * gq.PW));
+    }
     env->g = mcov::make_geometry(W, L);
     env->wall = wall_dev;
     env->pos = pos_dev;

@@ -30,52 +30,79 @@ def env_from_torchrun():
 
 
 class StatsReducer:
-    """Double-buffered all-reduce of the per-step statistics vector on a side stream, so the tiny,
-    latency-bound collective overlaps the next step kernel (CUDA) — or a plain blocking all-reduce
-    (CPU / gloo)."""
+    """All-reduce of every step's statistics vector.
 
-    def __init__(self, device, world=None, group=None):
+    CUDA, world > 1: the vectors of ``block`` consecutive steps are collected in a [block, 8] device block
+    and reduced with ONE collective on a side stream while the next block's steps run (two blocks, event
+    hand-over), so the latency-bound collective neither sits between two step kernels nor costs a launch per
+    step; ``block=1`` reduces after every step.  Every step's vector is reduced either way — ``last_block()``
+    exposes the per-step global rows of the block that completed last, ``total`` their running sum.
+    CPU / gloo: a plain blocking all-reduce with the same block semantics."""
+
+    def __init__(self, device, world=None, group=None, block=1):
         import torch
         import torch.distributed as dist
         self.torch, self.dist, self.group = torch, dist, group
         self.device = torch.device(device)
         self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.cuda = self.device.type == "cuda"
-        self.bufs = [torch.zeros(8, dtype=torch.float64, device=self.device) for _ in range(2)]
+        self.block = max(1, int(block))
+        self.blocks = [torch.zeros((self.block, 8), dtype=torch.float64, device=self.device) for _ in range(2)]
         self.total = torch.zeros(8, dtype=torch.float64, device=self.device)
         self.k = 0
-        if self.cuda and self.world > 1:
+        self._last = None
+        self.overlap = self.cuda and self.world > 1
+        if self.overlap:
             self.side = torch.cuda.Stream(device=self.device)
             self.ev_ready = [torch.cuda.Event() for _ in range(2)]
             self.ev_done = [torch.cuda.Event() for _ in range(2)]
 
     def buffer(self):
-        """The statistics buffer the next step must write (waits until its previous all-reduce is done)."""
-        b = self.k & 1
-        if self.cuda and self.world > 1 and self.k >= 2:
-            self.torch.cuda.current_stream(self.device).wait_event(self.ev_done[b])
-        return self.bufs[b]
+        """The 8-double row the next step must write (waits until the block's previous reduction is done)."""
+        blk, row = (self.k // self.block) & 1, self.k % self.block
+        if self.overlap and row == 0 and self.k >= 2 * self.block:
+            self.torch.cuda.current_stream(self.device).wait_event(self.ev_done[blk])
+        return self.blocks[blk][row]
+
+    def _reduce(self, blk, rows):
+        view = self.blocks[blk][:rows]
+        if self.overlap:
+            main = self.torch.cuda.current_stream(self.device)
+            self.ev_ready[blk].record(main)
+            with self.torch.cuda.stream(self.side):
+                self.side.wait_event(self.ev_ready[blk])
+                self.dist.all_reduce(view, group=self.group)
+                self.total.add_(view.sum(dim=0))
+                self.ev_done[blk].record(self.side)
+        else:
+            if self.world > 1:
+                self.dist.all_reduce(view, group=self.group)
+            self.total.add_(view.sum(dim=0))
+        self._last = view
 
     def submit(self):
         """Call after the step that wrote ``buffer()`` has been enqueued."""
-        b = self.k & 1
-        if self.world > 1 and self.cuda:
-            main = self.torch.cuda.current_stream(self.device)
-            self.ev_ready[b].record(main)
-            with self.torch.cuda.stream(self.side):
-                self.side.wait_event(self.ev_ready[b])
-                self.dist.all_reduce(self.bufs[b], group=self.group)
-                self.total.add_(self.bufs[b])
-                self.ev_done[b].record(self.side)
-        else:
-            if self.world > 1:
-                self.dist.all_reduce(self.bufs[b], group=self.group)
-            self.total.add_(self.bufs[b])
+        blk, row = (self.k // self.block) & 1, self.k % self.block
         self.k += 1
+        if row == self.block - 1:
+            self._reduce(blk, self.block)
+
+    def last_block(self):
+        """[rows, 8] global per-step statistics of the most recently reduced block (None before the first);
+        on CUDA valid once the side stream has passed ``ev_done`` — ``finish()`` or a stream wait."""
+        return self._last
+
+    def flush(self):
+        """Reduces a partially filled block now (end of a rollout); the next step starts a fresh block."""
+        rows = self.k % self.block
+        if rows:
+            self._reduce((self.k // self.block) & 1, rows)
+            self.k += self.block - rows
 
     def finish(self):
-        """Joins the side stream; returns the running global totals (dict of python floats)."""
-        if self.cuda and self.world > 1:
+        """Flushes, joins the side stream; returns the running global totals."""
+        self.flush()
+        if self.overlap:
             self.torch.cuda.current_stream(self.device).wait_stream(self.side)
         if self.cuda:
             self.torch.cuda.synchronize(self.device)

@@ -35,13 +35,13 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, total_envs, steps, out_dir):
+def _worker(rank, world, port, total_envs, steps, out_dir, block):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     lo, hi = shard_range(total_envs, rank, world)
-    red = StatsReducer("cpu", world=world)
+    red = StatsReducer("cpu", world=world, block=block)
     rng = np.random.default_rng(0)                     # same stream on every rank: global per-env stats
     for _ in range(steps):
         per_env = rng.integers(0, 5, size=(total_envs, 8)).astype(np.float64)
@@ -53,9 +53,11 @@ def _worker(rank, world, port, total_envs, steps, out_dir):
     dist.destroy_process_group()
 
 
-def test_stats_allreduce_gloo_world2(tmp_path):
-    world, total_envs, steps = 2, 37, 5
-    mp.spawn(_worker, args=(world, _free_port(), total_envs, steps, str(tmp_path)), nprocs=world, join=True)
+@pytest.mark.parametrize("block", [1, 3, 8])
+def test_stats_allreduce_gloo_world2(tmp_path, block):
+    world, total_envs, steps = 2, 37, 7                # 7 steps: blocks of 3 and 8 end on a partial block
+    mp.spawn(_worker, args=(world, _free_port(), total_envs, steps, str(tmp_path), block), nprocs=world,
+             join=True)
     rng = np.random.default_rng(0)
     want = np.zeros(8)
     for _ in range(steps):
