@@ -27,7 +27,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-STATS_BLOCK = 8        # steps per statistics all-reduce at N > 1 (every step's vector is reduced, 8 per call)
+# steps per statistics all-reduce at N > 1 (every step's vector is reduced, STATS_BLOCK of them per call)
+STATS_BLOCK = max(1, int(os.environ.get("MCOV_STATS_BLOCK", "8")))
 METRIC = "agent-steps/sec (batched env step, 1/2/4/8 B200) and % of HBM roofline"
 UNIT = "agent-steps/s"
 
