@@ -249,7 +249,7 @@ def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, f
     from marl_coverage_b200.sharding import StatsReducer
     dev = env.device
     # NCCL SUM of every step's 64-byte statistics vector, STATS_BLOCK steps per collective on a side stream
-    red = StatsReducer(dev, world=world, block=STATS_BLOCK if world > 1 else 1)
+    red = StatsReducer(dev, world=world, block=STATS_BLOCK)
     main = torch.cuda.current_stream(dev)
 
     def one(k):
@@ -269,8 +269,8 @@ def timed_steps(torch, dist, env, acts, warmup, steps, world, stats_ring=None, f
         e0.record(main)
         for k in range(warmup, warmup + steps):
             one(k)
+        red.flush()                                      # the timed steps' statistics are reduced inside the region
         if world > 1:
-            red.flush()                                  # the timed steps' statistics are reduced inside the region
             main.wait_stream(red.side)
         e1.record(main)
         torch.cuda.synchronize(dev)

@@ -72,12 +72,12 @@ class StatsReducer:
             with self.torch.cuda.stream(self.side):
                 self.side.wait_event(self.ev_ready[blk])
                 self.dist.all_reduce(view, group=self.group)
-                self.total.add_(view.sum(dim=0))
+                self.total.add_(view[0] if rows == 1 else view.sum(dim=0))
                 self.ev_done[blk].record(self.side)
         else:
             if self.world > 1:
                 self.dist.all_reduce(view, group=self.group)
-            self.total.add_(view.sum(dim=0))
+            self.total.add_(view[0] if rows == 1 else view.sum(dim=0))
         self._last = view
 
     def submit(self):
