@@ -73,3 +73,27 @@ def test_rollout_in_a_cuda_graph_equals_eager(kind):
             assert torch.equal(stats_log[t], eager.stats)
             episodes += float(eager.stats[0].item())
     assert episodes > 0, "the rollout must cross auto-resets inside the graph"
+
+
+def test_step_into_caller_result_buffers():
+    """step(results=...) writes reward / reward64 / done / stats into the caller's second buffer set (what the
+    double-buffered host loop of bench.py uses) and leaves the env's own tensors alone."""
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, load_grid_set
+    grids = load_grid_set("bg2_100x100", 3)
+    a = VecDecGridRL(grids, DEC, num_envs=50, auto_reset=True, truncate_steps=30, seed=2)
+    b = VecDecGridRL(grids, DEC, num_envs=50, auto_reset=True, truncate_steps=30, seed=2)
+    a.reset(seed=5)
+    b.reset(seed=5)
+    res = [b.make_result_buffers() for _ in range(2)]
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(1)
+    for t in range(40):
+        act = torch.randint(0, 4, (50, 4), dtype=torch.uint8, device="cuda", generator=gen)
+        oa, ra, da = a.step(act, want_stats=True)
+        keep = (b.reward.clone(), b.done.clone(), b.stats.clone())
+        ob, rb, db = b.step(act, want_stats=True, results=res[t & 1])
+        assert rb is res[t & 1]["reward"] and db is res[t & 1]["done"]
+        assert torch.equal(oa, ob) and torch.equal(ra, rb) and torch.equal(da, db)
+        assert torch.equal(a.reward64, res[t & 1]["reward64"]) and torch.equal(a.stats, res[t & 1]["stats"])
+        assert torch.equal(b.reward, keep[0]) and torch.equal(b.done, keep[1]) and torch.equal(b.stats, keep[2])
