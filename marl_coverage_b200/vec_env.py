@@ -117,11 +117,31 @@ class _VecEnv:
         if seed is None:
             seed = (self.seed + 0x9E3779B97F4A7C15 * self._reset_calls) & 0xFFFFFFFFFFFFFFFF
         self._reset_calls += 1
+        self._last_seed = int(seed)
         with torch.cuda.device(self.device):
             _lib.check(self._lib.mcov_reset(self._handle, _ptr(mk), _ptr(mi), _ptr(sx),
                                             C.c_uint64(int(seed)), obs.data_ptr(), self._stream()))
         self._keep = (mi, sx, mk)           # keep inputs alive until the stream has consumed them
         return obs
+
+    def get_state(self):
+        """Checkpoint of the whole batch: the state arena (planes, headers, poses, thresholds, episode
+        counters), the last observation and the seed the fused auto-resets derive their draws from.
+        ``set_state`` of it resumes the rollout bit for bit (tests/test_graph_gpu.py)."""
+        return {"arena": self._arena.clone(), "obs": self.obs.clone(), "seed": getattr(self, "_last_seed", None),
+                "reset_calls": self._reset_calls}
+
+    def set_state(self, state):
+        import torch
+        if state["arena"].numel() != self._arena.numel() or tuple(state["obs"].shape) != tuple(self.obs.shape):
+            raise ValueError("state belongs to an env batch of a different shape")
+        if state["seed"] is not None:
+            # a reset with an all-zero mask touches no env but re-arms the library's auto-reset seed
+            self.reset(mask=torch.zeros((self.num_envs,), dtype=torch.uint8, device=self.device),
+                       seed=state["seed"])
+        self._arena.copy_(state["arena"])
+        self.obs.copy_(state["obs"])
+        self._reset_calls = int(state["reset_calls"])
 
     def make_result_buffers(self):
         """A second set of per-step outputs for ``step(results=...)``: lets a caller double-buffer the

@@ -97,3 +97,37 @@ def test_step_into_caller_result_buffers():
         assert torch.equal(oa, ob) and torch.equal(ra, rb) and torch.equal(da, db)
         assert torch.equal(a.reward64, res[t & 1]["reward64"]) and torch.equal(a.stats, res[t & 1]["stats"])
         assert torch.equal(b.reward, keep[0]) and torch.equal(b.done, keep[1]) and torch.equal(b.stats, keep[2])
+
+
+@pytest.mark.parametrize("kind", ["dec", "super"])
+def test_get_set_state_resumes_a_rollout(kind):
+    """Checkpoint / resume: a rollout continued from get_state() in ANOTHER env object repeats bit for bit,
+    fused auto-resets (device RNG) included."""
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, load_grid_set
+    grids = load_grid_set("bg2_100x100", 4)
+    cfg = dict(SUPER) if kind == "super" else dict(DEC)
+    cls = VecSuperGridRL if kind == "super" else VecDecGridRL
+    E, N = 97, cfg["numrobot"]
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(11)
+    acts = torch.randint(0, 4, (70, E, N), dtype=torch.uint8, device="cuda", generator=gen)
+    a = cls(grids, cfg, num_envs=E, auto_reset=True, truncate_steps=30, seed=3)
+    a.reset()
+    for t in range(20):
+        a.step(acts[t], want_stats=True)
+    snap = a.get_state()
+    want = []
+    for t in range(20, 70):
+        o, r, d = a.step(acts[t], want_stats=True)
+        want.append((o.clone(), a.reward64.clone(), d.clone(), a.stats.clone()))
+    assert sum(float(w[3][0]) for w in want) > 0                      # episodes ended and were re-seeded
+    b = cls(grids, cfg, num_envs=E, auto_reset=True, truncate_steps=30, seed=999)
+    b.reset()
+    b.step(acts[5])
+    b.set_state(snap)
+    assert torch.equal(b.obs, snap["obs"]) and torch.equal(b.positions(), a.__class__.positions(b))
+    for k, t in enumerate(range(20, 70)):
+        o, r, d = b.step(acts[t], want_stats=True)
+        assert torch.equal(o, want[k][0]) and torch.equal(b.reward64, want[k][1]), (kind, t)
+        assert torch.equal(d, want[k][2]) and torch.equal(b.stats, want[k][3]), (kind, t)
