@@ -176,31 +176,32 @@ __global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams
 // flat byte stream (row starts are not 4-byte aligned in general: head / tail bytes go out singly).
 constexpr int RENDER_THREADS = 256;
 
+// One output row = the expanded row image in shared memory (`rowbuf`, or zeros), shifted to the row's own
+// 4-byte phase: word k of the row is bytes [head + 4k, head + 4k + 4) of the image, i.e. a funnel shift of two
+// aligned shared-memory words.
 __device__ __forceinline__ void render_store_row(uint8_t* out, long long row_start, int row_bytes,
-                                                 const uint16_t* ymap, const uint8_t* col, bool zero) {
+                                                 const uint8_t* rowbuf, bool zero) {
     const int head = (int)((4 - (row_start & 3)) & 3);
-    auto byte_at = [&](int r) -> uint32_t {
-        if (zero) return 0u;
-        const int j = r / 3, ch = r - 3 * j;
-        const uint32_t c = ymap[j];
-        return c == 0xffffu ? 0u : (uint32_t)col[c * 3 + ch];
-    };
-    for (int r = threadIdx.x; r < head && r < row_bytes; r += RENDER_THREADS) out[row_start + r] = (uint8_t)byte_at(r);
+    for (int r = threadIdx.x; r < head && r < row_bytes; r += RENDER_THREADS)
+        out[row_start + r] = zero ? (uint8_t)0 : rowbuf[r];
     const int words = (row_bytes - head) >> 2;
     uint32_t* out32 = reinterpret_cast<uint32_t*>(out + row_start + head);
+    const uint32_t* rb32 = reinterpret_cast<const uint32_t*>(rowbuf);
+    const int sh = 8 * head;                                   // head < 4: image words are read at byte phase `head`
     for (int w = threadIdx.x; w < words; w += RENDER_THREADS) {
-        const int r = head + 4 * w;
-        const uint32_t v = byte_at(r) | (byte_at(r + 1) << 8) | (byte_at(r + 2) << 16) | (byte_at(r + 3) << 24);
+        uint32_t v = 0;
+        if (!zero) v = head ? __funnelshift_r(rb32[w], rb32[w + 1], sh) : rb32[w];
         __stcs(out32 + w, v);
     }
     for (int r = head + 4 * words + threadIdx.x; r < row_bytes; r += RENDER_THREADS)
-        out[row_start + r] = (uint8_t)byte_at(r);
+        out[row_start + r] = zero ? (uint8_t)0 : rowbuf[r];
 }
 
 __global__ void __launch_bounds__(RENDER_THREADS) render_kernel(RenderParams p) {
     extern __shared__ __align__(16) unsigned char rsm[];
     uint16_t* ymap = reinterpret_cast<uint16_t*>(rsm);                     // [out_w] column -> cell y (0xffff: border)
     uint8_t* col = rsm + ((2 * p.out_w + 15) & ~15);                       // [L][3] colours of the current cell row
+    uint8_t* rowbuf = col + ((3 * p.g.L + 15) & ~15);                      // [row_bytes + 8] the expanded pixel row
     const int W = p.g.W, L = p.g.L, s = p.scale;
     for (int j = threadIdx.x; j < p.out_w; j += RENDER_THREADS) {
         const int jj = p.flip ? p.out_w - 1 - j : j;                       // cv2.flip(image, 1), dec_grid_rl.py:593
@@ -212,9 +213,10 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_kernel(RenderParams p) 
         const int f = item / (W + 1), x = item - f * (W + 1);
         const int e = p.env_ids ? p.env_ids[f] : f;
         const long long frame0 = (long long)f * p.out_h * row_bytes;
-        __syncthreads();                                                   // ymap ready / previous col consumed
+        __syncthreads();                                                   // ymap ready / previous row image consumed
         if (x == W) {
-            for (int i = W * s; i < p.out_h; ++i) render_store_row(p.out, frame0 + (long long)i * row_bytes, row_bytes, ymap, col, true);
+            for (int i = W * s; i < p.out_h; ++i)
+                render_store_row(p.out, frame0 + (long long)i * row_bytes, row_bytes, rowbuf, true);
             continue;
         }
         const int16_t* pos = reinterpret_cast<const int16_t*>(p.hdr + (size_t)e * p.hdr_stride + p.off_pos);
@@ -237,8 +239,17 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_kernel(RenderParams p) 
             col[3 * y + 2] = (uint8_t)((obst ? 255u : 0u) + (cov ? 255u : 0u));
         }
         __syncthreads();
+        // expand once: pixel j takes the colour of cell ymap[j]; the s output rows then only copy
+        for (int j = threadIdx.x; j < p.out_w + 3; j += RENDER_THREADS) {
+            const uint32_t c = j < p.out_w ? ymap[j] : 0xffffu;
+            const bool in = c != 0xffffu;
+            rowbuf[3 * j + 0] = in ? col[3 * c + 0] : (uint8_t)0;
+            rowbuf[3 * j + 1] = in ? col[3 * c + 1] : (uint8_t)0;
+            rowbuf[3 * j + 2] = in ? col[3 * c + 2] : (uint8_t)0;
+        }
+        __syncthreads();
         for (int i = x * s; i < x * s + s; ++i)
-            render_store_row(p.out, frame0 + (long long)i * row_bytes, row_bytes, ymap, col, false);
+            render_store_row(p.out, frame0 + (long long)i * row_bytes, row_bytes, rowbuf, false);
     }
 }
 
@@ -255,7 +266,8 @@ cudaError_t launch_render(const RenderParams& p, int num_sms, cudaStream_t st) {
     const int items = p.n * (p.g.W + 1);
     int grid = num_sms * 8;
     if (grid > items) grid = items;
-    const size_t smem = ((2 * (size_t)p.out_w + 15) & ~(size_t)15) + 3 * (size_t)p.g.L;
+    const size_t smem = ((2 * (size_t)p.out_w + 15) & ~(size_t)15) + ((3 * (size_t)p.g.L + 15) & ~(size_t)15) +
+                        3 * ((size_t)p.out_w + 3) + 16;
     render_kernel<<<grid, RENDER_THREADS, smem, st>>>(p);
     return cudaGetLastError();
 }
