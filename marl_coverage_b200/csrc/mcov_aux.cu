@@ -32,7 +32,10 @@ __device__ __forceinline__ int block_sum(int v, int* red) {
     return t;
 }
 
-__global__ void __launch_bounds__(SIM_THREADS, 4) sim_lookahead_kernel(SimParams p) {
+#ifndef MCOV_SIM_MINB
+#define MCOV_SIM_MINB 6
+#endif
+__global__ void __launch_bounds__(SIM_THREADS, MCOV_SIM_MINB) sim_lookahead_kernel(SimParams p) {
     __shared__ int s_first;                    // raster index of the robot in the position plane
     __shared__ int s_pos[2];                   // pose after the move
     __shared__ int s_red[SIM_THREADS / 32];
@@ -256,7 +259,7 @@ __global__ void __launch_bounds__(RENDER_THREADS) render_kernel(RenderParams p) 
 }  // namespace
 
 cudaError_t launch_sim_lookahead(const SimParams& p, int num_sms, cudaStream_t st) {
-    int grid = num_sms * 4;
+    int grid = num_sms * MCOV_SIM_MINB;
     if (grid > p.B) grid = p.B;
     sim_lookahead_kernel<<<grid, SIM_THREADS, 0, st>>>(p);
     return cudaGetLastError();
