@@ -90,7 +90,10 @@ int grid_for(long long items) {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     long long blocks = (items + 255) / 256;
-    const long long cap = (long long)sms * 8;
+#ifndef MCOV_REPLAY_CAP
+#define MCOV_REPLAY_CAP 64
+#endif
+    const long long cap = (long long)sms * MCOV_REPLAY_CAP;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return (int)blocks;
