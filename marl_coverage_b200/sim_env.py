@@ -8,7 +8,7 @@ library and a device the constructors raise.
 
 The reference function cannot run at its HEAD (``np.asscalar`` was removed from numpy; ``percent_covered``
 is called without its ``grid`` argument, sim_env.py:146-147,187,248); both are read the way the
-surrounding code intends, and ``tools/pin_sim_render.py`` pins that reading against the reference with
+surrounding code intends, and ``tests/golden/pin_sim_render.py`` pins that reading against the reference with
 exactly those two shims.
 """
 import ctypes as C

@@ -7,9 +7,9 @@ ExistentialRobotics/MARL-Coverage.  Only ``tests/``, ``__graft_entry__.smoke()``
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import it; the product path
 (``marl_coverage_b200``) never does and fails loudly without its CUDA library.
 
-Parity status: PINNED.  ``tools/pin_oracle.py`` runs this file step-for-step against the live,
+Parity status: PINNED.  ``tests/golden/pin_oracle.py`` runs this file step-for-step against the live,
 unmodified reference (imported from /root/reference in the build container) over the config matrix
-listed in ``tests/golden/PIN_REPORT.json``; ``tools/make_golden.py`` records reference traces into
+listed in ``tests/golden/PIN_REPORT.json``; ``tests/golden/make_golden.py`` records reference traces into
 ``tests/golden/*.npz`` and ``tests/test_oracle_golden.py`` replays them against this file on every
 CPU test run.  The reference itself ships no tests for this path.
 
@@ -691,7 +691,7 @@ def sim_lookahead(state4, action, grid, env_config, done_thresh=None):
       * ``np.asscalar`` (sim_env.py:146-147) was removed in numpy 1.23 -> ``.item()``;
       * ``self.percent_covered(state)`` (sim_env.py:187) omits the ``grid`` argument of
         ``percent_covered(self, state, grid)`` (sim_env.py:248) -> the step's own ``grid``.
-    ``tools/pin_sim_render.py`` runs the reference with exactly those two shims to pin this function.
+    ``tests/golden/pin_sim_render.py`` runs the reference with exactly those two shims to pin this function.
     Moves use SuperGridRL's mapping 0:x-1 1:x+1 2:y+1 3:y-1; only obstacles block (isOccupied,
     sim_env.py:210-228); the distance plane is carried through unchanged (not recomputed); the float64
     reward is accumulated in the reference's order: move term, then footprint cells in raster order.

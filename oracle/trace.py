@@ -2,7 +2,7 @@
 
 A trace is one *session* of one env object: a list of ops (``reset`` with an injected map index
 and start poses, or ``step`` with a base-4 joint action / the -1 sentinel) together with what the
-reference returned / held after each op.  ``tools/make_golden.py`` records them from the live
+reference returned / held after each op.  ``tests/golden/make_golden.py`` records them from the live
 reference; ``tests/`` replays them against the oracle (CPU) and the CUDA env (GPU).
 
 File format: ``np.savez_compressed`` with the keys documented in ``Trace``.
@@ -144,7 +144,7 @@ class Recorder:
 
 
 # ---------------------------------------------------------------------------------------------
-# snapshots of the ORACLE env (the reference-side twin lives in tools/make_golden.py)
+# snapshots of the ORACLE env (the reference-side twin lives in tests/golden/make_golden.py)
 # ---------------------------------------------------------------------------------------------
 
 def snap_oracle(env, kind, obs_or_state, reward, done):

@@ -5,7 +5,7 @@ Each trace is a session of one reference env object driven with seeded base-4 in
 poses are read back from the reference after every reset and stored, so the replaying side injects
 them instead of reproducing numpy's Mersenne-Twister rejection sampling.
 
-Outputs tests/golden/<name>.npz (committed; small).  Usage:  python tools/make_golden.py
+Outputs tests/golden/<name>.npz (committed; small).  Usage:  python tests/golden/make_golden.py
 """
 import os
 import sys
@@ -13,7 +13,7 @@ import sys
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ROOT = os.path.dirname(HERE)
+ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, HERE)
 sys.path.insert(0, ROOT)
 

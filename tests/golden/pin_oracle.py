@@ -5,7 +5,7 @@ the same integer (base-4) action stream, and compares after every reset/step:
 positions, reward, done flag, observation/state tensors, the per-robot free/obstacle planes,
 visited / observed-obstacle planes, adjacency, percent_covered and done_thresh.
 
-Writes tests/golden/PIN_REPORT.json (committed).  Usage:  python tools/pin_oracle.py
+Writes tests/golden/PIN_REPORT.json (committed).  Usage:  python tests/golden/pin_oracle.py
 """
 import json
 import os
@@ -15,7 +15,7 @@ import time
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ROOT = os.path.dirname(HERE)
+ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, HERE)
 sys.path.insert(0, ROOT)
 

@@ -9,7 +9,7 @@ Shims, all outside the reference's files:
     the array, ``surfarray.array3d`` returns it as uint8 (pygame truncates float pixel values; every
     value render() produces is an integer <= 255).
 
-Outputs: tests/golden/sim_lookahead.npz, tests/golden/render_frames.npz.  Usage: python tools/pin_sim_render.py
+Outputs: tests/golden/sim_lookahead.npz, tests/golden/render_frames.npz.  Usage: python tests/golden/pin_sim_render.py
 """
 import os
 import sys
@@ -18,7 +18,7 @@ import zlib
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ROOT = os.path.dirname(HERE)
+ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, HERE)
 sys.path.insert(0, ROOT)
 

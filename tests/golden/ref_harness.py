@@ -6,8 +6,8 @@ imports ``pygame`` and ``matplotlib`` at module top level
 for a window and plots; neither is installed here, so two empty stub modules are placed in
 ``sys.modules`` before the import.  Nothing under /root/reference is copied or modified.
 
-/root/reference does not exist on the GPU box: only ``tools/make_golden.py`` and
-``tools/pin_oracle.py`` (run here, outputs committed under tests/golden/) import this file.
+/root/reference does not exist on the GPU box: only ``tests/golden/make_golden.py`` and
+``tests/golden/pin_oracle.py`` (run here, outputs committed under tests/golden/) import this file.
 """
 import contextlib
 import io

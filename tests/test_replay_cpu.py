@@ -1,5 +1,5 @@
 """The oracle ring buffer against golden vectors recorded from the reference's ReplayBuffer
-(tools/make_golden_replay.py), and — when /root/reference is present — against the reference live."""
+(tests/golden/make_golden_replay.py), and — when /root/reference is present — against the reference live."""
 import os
 import sys
 

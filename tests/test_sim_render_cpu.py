@@ -1,5 +1,5 @@
 """CPU checks for SURVEY §8f ranks 3-4: the oracle's SuperGrid_Sim lookahead and render() frames against the
-golden vectors tools/pin_sim_render.py recorded from the live reference (sim_env.py with the two
+golden vectors tests/golden/pin_sim_render.py recorded from the live reference (sim_env.py with the two
 documented shims; render() with the pygame stub)."""
 import json
 import os

@@ -14,7 +14,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 import ref_harness as rh  # noqa: E402
 from PIL import Image  # noqa: E402
 
