@@ -74,6 +74,41 @@ def test_vectorised_rows_and_errors():
                                 None) == -2
 
 
+@pytest.mark.parametrize("shape", [(3, 11, 11), (17,), (3, 7, 7), (5, 5, 5)])
+def test_unaligned_rows_every_phase(shape):
+    """Rows whose length is not a multiple of 4 floats (the reference's 363-float state[0] rows) go through
+    the shifted 128-bit copy: every source / destination phase, strided sources, ring wrap, gather."""
+    import torch
+    from marl_coverage_b200 import ReplayBuffer
+    row = int(np.prod(shape))
+    g = torch.Generator(device="cuda")
+    g.manual_seed(row)
+    cap = 61
+    buf = ReplayBuffer(shape, 1, cap)
+    want_s = torch.zeros((cap, row), device="cuda")
+    want_n = torch.zeros((cap, row), device="cuda")
+    ptr = 0
+    for it, E in enumerate((7, 13, 29, 31, 5)):
+        stride = row + it                                        # 0..4 floats of padding: every source phase
+        st = torch.rand((E, stride), device="cuda", generator=g)
+        nx = torch.rand((E, stride), device="cuda", generator=g)
+        ac = torch.randint(0, 4, (E, 1), dtype=torch.uint8, device="cuda", generator=g)
+        rw = torch.rand((E,), device="cuda", generator=g)
+        dn = torch.zeros((E,), dtype=torch.uint8, device="cuda")
+        buf.addbatch(st, ac, rw, nx, dn, src_stride=stride)
+        rows = (ptr + torch.arange(E, device="cuda")) % cap
+        want_s[rows] = st[:, :row]
+        want_n[rows] = nx[:, :row]
+        ptr = (ptr + E) % cap
+    assert buf._ptr == ptr
+    assert torch.equal(buf._state.reshape(cap, row), want_s)
+    assert torch.equal(buf._nextstate.reshape(cap, row), want_n)
+    idx = np.array([0, 60, 17, 17, 33, 1, 59, 2, 44], np.int64)
+    out = buf.gather(idx)
+    assert torch.equal(out[0].reshape(len(idx), row), want_s[torch.from_numpy(idx).cuda()])
+    assert torch.equal(out[3].reshape(len(idx), row), want_n[torch.from_numpy(idx).cuda()])
+
+
 CFG = dict(numrobot=3, maxsteps=1000, collision_penalty=5, done_thresh=0.6, done_incr=0.0, terminal_reward=30,
            dist_reward=0, train_maxsteps=25, test_maxsteps=25, egoradius=3, mini_map_rad=0, comm_radius=0,
            allow_comm=0, map_sharing=0, single_square_tool=0, dijkstra_input=0, sensor_type="square_sensor",
