@@ -6,6 +6,8 @@ positions, reward, done flag, observation/state tensors, the per-robot free/obst
 visited / observed-obstacle planes, adjacency, percent_covered and done_thresh.
 
 Writes tests/golden/PIN_REPORT.json (committed).  Usage:  python tests/golden/pin_oracle.py
+``--check`` runs the same comparison without touching the report (tests/test_oracle_golden.py uses it wherever
+/root/reference is present).
 """
 import json
 import os
@@ -215,8 +217,9 @@ def main():
         report["cases"][name] = res
         print(name, res["status"], {k: v for k, v in res.items() if k not in ("config",)})
     report["all_match"] = ok
-    with open(os.path.join(ROOT, "tests", "golden", "PIN_REPORT.json"), "w") as f:
-        json.dump(report, f, indent=1, sort_keys=True)
+    if "--check" not in sys.argv[1:]:
+        with open(os.path.join(ROOT, "tests", "golden", "PIN_REPORT.json"), "w") as f:
+            json.dump(report, f, indent=1, sort_keys=True)
     return 0 if ok else 1
 
 

@@ -183,12 +183,17 @@ def pin_render():
         meta.append({"name": name, "kind": kind, "cfg": cfg, "map_index": mi})
         print("render %-14s frame %s matches the oracle" % (name, want.shape))
     frames["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+    if CHECK_ONLY:
+        return
     path = os.path.join(OUT, "render_frames.npz")
     np.savez_compressed(path, **frames)
     print("wrote %s (%.1f kB)" % (path, os.path.getsize(path) / 1e3))
 
 
+CHECK_ONLY = "--check" in sys.argv[1:]        # compare only, leave the committed fixtures alone
+
 if __name__ == "__main__":
     specs, cases = pin_sim()
-    save_sim(specs, cases)
+    if not CHECK_ONLY:
+        save_sim(specs, cases)
     pin_render()

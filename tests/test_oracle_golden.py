@@ -28,6 +28,21 @@ def test_pin_report_all_match():
     assert all(c["status"] == "match" for c in rep["cases"].values())
 
 
+def test_oracle_matches_live_reference():
+    """Where the reference is present (the build container, never the GPU box) the pin is re-run live: the
+    unmodified reference and the oracle side by side over all pinned configurations, in a subprocess so the
+    pygame / matplotlib stubs the reference needs do not leak into this process."""
+    import subprocess
+    import sys
+    ref = os.environ.get("MCOV_REFERENCE_ROOT", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "Environments")):
+        pytest.skip("reference not present")
+    res = subprocess.run([sys.executable, os.path.join(GOLDEN_DIR, "pin_oracle.py"), "--check"],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert res.stdout.count(" match ") >= 20 and "MISMATCH" not in res.stdout
+
+
 def test_golden_covers_edge_cases():
     """The fixtures must actually contain the situations Appendix A of SURVEY.md lists."""
     tr = Trace.load(os.path.join(GOLDEN_DIR, "dec_c2_square_100.npz"))

@@ -6,6 +6,7 @@ import os
 import zlib
 
 import numpy as np
+import pytest
 
 from conftest import GOLDEN_DIR
 from oracle import coverage_oracle as oc
@@ -73,3 +74,16 @@ def test_sim_lookahead_does_not_mutate_and_terminal():
     assert r == -5 + 8 + 30                             # 8 free cells of the 3x3; 8/41 >= 0.19: terminal bonus
     cfg["done_thresh"] = 0.2
     assert oc.sim_lookahead(st, 2, grid, cfg)[1] == -5 + 8
+
+
+def test_oracle_matches_live_reference():
+    """Re-runs the pin against the live reference where it is present (never on the GPU box)."""
+    import subprocess
+    import sys
+    ref = os.environ.get("MCOV_REFERENCE_ROOT", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "Environments")):
+        pytest.skip("reference not present")
+    res = subprocess.run([sys.executable, os.path.join(GOLDEN_DIR, "pin_sim_render.py"), "--check"],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert res.stdout.count("matches the oracle") >= 6
