@@ -87,3 +87,29 @@ def test_oracle_matches_live_reference():
                          capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert res.stdout.count("matches the oracle") >= 6
+
+
+def test_lookahead_agrees_with_env_step():
+    """Two independently pinned restatements against each other: for one robot, SuperGrid_Sim's lookahead of
+    the env's state is the env's own next state (position / seen-obstacle / not-covered planes) and reward —
+    except the env's first-step motion penalty (quirk A.2.6), which the simulator does not have."""
+    from marl_coverage_b200 import load_grid_set
+    grids = load_grid_set("bg2_100x100", 3)
+    cfg = dict(numrobot=1, train_maxsteps=1000, test_maxsteps=1000, collision_penalty=5, senseradius=2,
+               free_penalty=0.25, done_thresh=1, done_incr=0, terminal_reward=30, dist_reward=0, use_scanning=0)
+    rng = np.random.RandomState(4)
+    np.random.seed(4)
+    env = oc.OracleSuperGridRL(grids, cfg)
+    for mi in range(len(grids)):
+        state = env.reset(False, None, map_index=mi)[0][0]      # ((planes, step), grid)
+        first = env._never_stepped
+        for t in range(120):
+            a = int(rng.randint(0, 4))
+            want, want_r = oc.sim_lookahead(state, a, env._grid, cfg)
+            nxt, r, done = env.step(a)
+            nxt = nxt[0]
+            assert np.array_equal(nxt[:3], want[:3]), (mi, t)
+            assert r == want_r + (-1 if first else 0), (mi, t, r, want_r)
+            first = False
+            state = nxt
+            assert not done
