@@ -102,6 +102,33 @@ class _VecEnv:
         except Exception:
             pass
 
+    def _check_obs_out(self, t):
+        """A caller-supplied observation buffer goes to the kernel as a raw pointer: refuse anything the kernel
+        would overrun or misread instead of corrupting device memory."""
+        import torch
+        n = int(np.prod(self.obs_shape))
+        if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+                and t.numel() == n and (self.device.index is None or t.device.index == self.device.index)):
+            raise ValueError("out must be a contiguous float32 CUDA tensor of %d elements %s on %s"
+                             % (n, self.obs_shape, self.device))
+        return t
+
+    def _check_results(self, res):
+        import torch
+        seen = self.__dict__.setdefault("_results_ok", [])       # validated once per buffer set, not per step
+        if any(res is r for r in seen):
+            return res
+        E = self.num_envs
+        want = (("reward", torch.float32, E), ("reward64", torch.float64, E), ("done", torch.uint8, E),
+                ("stats", torch.float64, _lib.STATS_LEN))
+        for key, dt, n in want:
+            t = res[key]
+            if not (t.is_cuda and t.dtype == dt and t.is_contiguous() and t.numel() == n):
+                raise ValueError("results[%r] must be a contiguous %s CUDA tensor of %d elements" % (key, dt, n))
+        del seen[3:]
+        seen.insert(0, res)
+        return res
+
     # -- the hot path -----------------------------------------------------------------------------
     def reset(self, map_idx=None, start_xy=None, mask=None, seed=None, out=None):
         """Starts new episodes (all envs, or those where ``mask`` is non-zero).
@@ -110,7 +137,7 @@ class _VecEnv:
         start_xy int16 [E, N, 2] env coordinates or None (device RNG: uniform distinct walkable cells)
         Returns the float32 CUDA observation tensor (written in place into ``out`` or ``self.obs``)."""
         import torch
-        obs = self.obs if out is None else out
+        obs = self.obs if out is None else self._check_obs_out(out)
         mi = self._as_dev(map_idx, torch.int32, (self.num_envs,))
         sx = self._as_dev(start_xy, torch.int16, (self.num_envs, self.num_robots, 2))
         mk = self._as_dev(mask, torch.uint8, (self.num_envs,))
@@ -163,7 +190,9 @@ class _VecEnv:
         env's own tensors.
         Returns (obs float32 CUDA, reward float32 [E] CUDA, done uint8 [E] CUDA)."""
         import torch
-        obs = self.obs if out is None else out
+        obs = self.obs if out is None else self._check_obs_out(out)
+        if results is not None:
+            self._check_results(results)
         rew = self.reward if results is None else results["reward"]
         rew64 = self.reward64 if results is None else results["reward64"]
         dn = self.done if results is None else results["done"]
@@ -173,6 +202,8 @@ class _VecEnv:
             act = torch.as_tensor(np.asarray(act))
         if act.dtype == torch.int64 and act.dim() == 1:
             fmt = _lib.ACT_I64_BASE4
+            if act.shape[0] != self.num_envs:
+                raise ValueError("base-4 joint actions must be int64 [E] = [%d]" % self.num_envs)
         elif act.dim() == 2:
             fmt = _lib.ACT_U8_PER_ROBOT
             if act.dtype != torch.uint8:
@@ -194,7 +225,7 @@ class _VecEnv:
 
     def observe(self, out=None):
         import torch
-        obs = self.obs if out is None else out
+        obs = self.obs if out is None else self._check_obs_out(out)
         with torch.cuda.device(self.device):
             _lib.check(self._lib.mcov_observe(self._handle, obs.data_ptr(), self._stream()))
         return obs
@@ -216,6 +247,9 @@ class _VecEnv:
         n = self.num_envs if ids is None else int(ids.numel())
         if out is None:
             out = torch.empty((n, h.value, w.value, 3), dtype=torch.uint8, device=self.device)
+        elif not (torch.is_tensor(out) and out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous()
+                  and out.numel() == n * h.value * w.value * 3):
+            raise ValueError("out must be a contiguous uint8 CUDA tensor [%d, %d, %d, 3]" % (n, h.value, w.value))
         with torch.cuda.device(self.device):
             _lib.check(self._lib.mcov_render(self._handle, _ptr(ids), n, out.data_ptr(), self._stream()))
         self._keep_ids = ids

@@ -131,3 +131,39 @@ def test_get_set_state_resumes_a_rollout(kind):
         o, r, d = b.step(acts[t], want_stats=True)
         assert torch.equal(o, want[k][0]) and torch.equal(b.reward64, want[k][1]), (kind, t)
         assert torch.equal(d, want[k][2]) and torch.equal(b.stats, want[k][3]), (kind, t)
+
+
+def test_caller_buffers_are_validated():
+    """Buffers that reach the kernels as raw pointers are checked on the host: a wrong size, dtype, layout or
+    device raises instead of overrunning device memory."""
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, load_grid_set
+    grids = load_grid_set("bg2_100x100", 2)
+    env = VecDecGridRL(grids, DEC, num_envs=6, seed=1)
+    env.reset(seed=3)
+    act = torch.zeros((6, 4), dtype=torch.uint8, device="cuda")
+    good = torch.empty_like(env.obs)
+    assert env.step(act, out=good)[0] is good                                       # accepted
+    bad_outs = [torch.empty(env.obs.numel() - 1, device="cuda"),                    # too small
+                torch.empty_like(env.obs, dtype=torch.float64),                     # wrong dtype
+                torch.empty(tuple(env.obs_shape) + (2,), device="cuda")[..., 0],    # not contiguous
+                torch.empty(tuple(env.obs_shape))]                                  # host memory
+    for bad in bad_outs:
+        with pytest.raises(ValueError):
+            env.step(act, out=bad)
+        with pytest.raises(ValueError):
+            env.observe(out=bad)
+        with pytest.raises(ValueError):
+            env.reset(out=bad)
+    with pytest.raises(ValueError):
+        env.step(torch.zeros((5,), dtype=torch.int64, device="cuda"))               # base-4 actions: wrong E
+    res = env.make_result_buffers()
+    res["done"] = torch.zeros((5,), dtype=torch.uint8, device="cuda")
+    with pytest.raises(ValueError):
+        env.step(act, results=res)
+    with pytest.raises(ValueError):
+        env.render(out=torch.empty((3,), dtype=torch.uint8, device="cuda"))
+    twin = VecDecGridRL(grids, DEC, num_envs=6, seed=1)                             # the refusals touched nothing
+    twin.reset(seed=3)
+    twin.step(act)
+    assert torch.equal(twin.step(act)[0], env.step(act)[0])
