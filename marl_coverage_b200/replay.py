@@ -62,6 +62,15 @@ class ReplayBuffer(object):
         if E > self._maxsize:
             raise ValueError("batch of %d rows exceeds the buffer capacity %d" % (E, self._maxsize))
         stride = self._row if src_stride is None else int(src_stride)
+        need = ((E - 1) * stride + self._row) * 4                   # bytes the kernel reads from each source
+        for name, t in (("state", state), ("next_state", next_state)):
+            if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float32):
+                raise ValueError("%s must be a float32 CUDA tensor" % name)
+            if stride < self._row or t.untyped_storage().nbytes() - t.storage_offset() * 4 < need:
+                raise ValueError("%s holds fewer than %d rows of %d floats at stride %d" % (name, E, self._row, stride))
+        if not (reward.is_cuda and reward.dtype == torch.float32 and reward.is_contiguous() and done.is_cuda
+                and done.numel() == E and action.is_cuda and action.numel() == E * self._adim):
+            raise ValueError("reward float32 [E], done [E] and action [E, %d] must be CUDA tensors" % self._adim)
         act = action if action.dtype in (torch.uint8, torch.float32) else action.to(torch.float32)
         act = act.contiguous()
         dn = done if done.dtype == torch.uint8 else done.to(torch.uint8)

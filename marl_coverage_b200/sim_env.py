@@ -60,6 +60,10 @@ class VecSuperGridSim:
         act = env._as_dev(actions, torch.uint8, (B,))
         mi = env._as_dev(map_idx, torch.int32, (B,))
         pxy = env._as_dev(pos_xy, torch.int16, (B, 2))
+        if out is not None and not inplace and not (
+                torch.is_tensor(out) and out.is_cuda and out.dtype == torch.float32 and out.is_contiguous()
+                and out.numel() == st.numel()):
+            raise ValueError("out must be a contiguous float32 CUDA tensor %s" % (tuple(st.shape),))
         nxt = st if inplace else (out if out is not None else torch.empty_like(st))
         r64 = torch.empty((B,), dtype=torch.float64, device=self.device)
         term = torch.empty((B,), dtype=torch.uint8, device=self.device)
