@@ -204,17 +204,21 @@ def run_reference(args):
     rates = []
     t0 = time.perf_counter()
     procs = None
+    walls = []
     for _ in range(min(steps, 6)):
+        t1 = time.perf_counter()
         r, procs = cpu_arm(kind, grid_name, cfg, sample_s, 0.5)
+        walls.append(time.perf_counter() - t1)
         rates.append(r)
         if time.perf_counter() - t0 > 150:
             break
     value = sum(rates) / len(rates)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": desc, "note": "CPU arm: numpy oracle port of the pure-Python reference env "
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(walls) / len(walls),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "note": "CPU arm (a step of this arm = one bounded sample, process start-up "
+                   "included in ms_per_step but not in the rate): numpy oracle port of the pure-Python reference env "
                    "(the reference needs /root/reference, absent on the GPU box); one env per process, "
                    "random base-4 actions, reset on done / train_maxsteps"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port",
