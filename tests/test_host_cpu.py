@@ -71,3 +71,30 @@ def test_algorithmic_bytes_match_survey():
     assert bench.alg_bytes_per_env_step(kind, cfg, 102, 102) == 7769
     kind, grid, E, cfg, _ = bench.WORKLOADS["c3"]
     assert bench.alg_bytes_per_env_step(kind, cfg, 258, 258) == 23341
+
+
+def test_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference runs on the host cores only: the JSON line must carry every key the driver
+    reads (metric / unit of BASELINE.json, cpu_baseline, e2e with zero copies, no GPU launches)."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "120",
+                          "--warmup", "0"], capture_output=True, text=True, timeout=300, cwd=root)
+    assert res.returncode == 0, res.stderr[-2000:]
+    lines = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    with open(os.path.join(root, "BASELINE.json")) as f:
+        base = json.load(f)
+    assert d["impl"] == "reference" and d["metric"] == base["metric"] and d["unit"] == "agent-steps/s"
+    for key in ("value", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                "dtype", "data", "config", "cpu_baseline", "e2e", "gpu_launches"):
+        assert key in d, key
+    assert d["value"] > 0 and d["ms_per_step"] > 0 and d["vs_baseline"] is None and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    assert "workload" in d["config"] and "model" not in d["config"]
