@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define MCOV_ABI_VERSION 5
+#define MCOV_ABI_VERSION 6
 #define MCOV_MAX_ROBOTS 32       /* base-4 joint actions live in an int64: 31 digits; lanes: 32 */
 #define MCOV_MAX_RADIUS 15       /* sensor range, egoradius, mini_map_rad: windows fit 32 bits  */
 #define MCOV_MAX_LASERS 1024
@@ -143,6 +143,15 @@ int mcov_set_lidar_beams(mcov_env* env, const double* beams_host, int num_lasers
 int mcov_pack_maps(const int8_t* cells_dev, int n_maps, int W, int L, int add_border,
                    uint32_t* wall_out_dev, uint32_t* pos_out_dev, int32_t* free_counts_out_dev,
                    void* stream);
+
+/* gridgen on the device (Utils/gridmaker.py:107-139): n_maps Bernoulli maps of W x L cells, every cell an
+ * obstacle with probability prob_obst and free (+1) otherwise, written straight into the packed planes
+ * mcov_pack_maps would produce for them (same add_border ring, same free counts) — no host grids, no copy.
+ * Same distribution as the reference's np.random.choice(a=[1.0, -1.0], p=[1 - p, p]), not numpy's stream:
+ * Philox4x32-10 keyed by `seed`, counter = (map, x, y / 4), so a map does not depend on n_maps or on the
+ * plane layout. */
+int mcov_gen_maps(int n_maps, int W, int L, int add_border, double prob_obst, uint64_t seed,
+                  uint32_t* wall_out_dev, uint32_t* pos_out_dev, int32_t* free_counts_out_dev, void* stream);
 
 /* Binds the packed map table (kept by reference; caller keeps it alive).  W, L are the
  * env-coordinate sizes (bordered for Dec). */

@@ -10,7 +10,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmcov_b200.so")
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 MAX_ROBOTS = 32
 MAX_RADIUS = 15
 STATS_LEN = 8
@@ -24,7 +24,7 @@ STATUS_NAMES = {0: "MCOV_OK", -1: "MCOV_ERR_BAD_CONFIG", -2: "MCOV_ERR_NULL", -3
 
 # every symbol include/mcov.h declares (tests check the .so exports exactly these)
 EXPORTS = ("mcov_abi_version", "mcov_last_error", "mcov_plane_geometry", "mcov_create",
-           "mcov_destroy", "mcov_set_lidar_beams", "mcov_pack_maps", "mcov_set_maps",
+           "mcov_destroy", "mcov_set_lidar_beams", "mcov_pack_maps", "mcov_gen_maps", "mcov_set_maps",
            "mcov_state_layout", "mcov_bind_state", "mcov_obs_shape", "mcov_reset", "mcov_step",
            "mcov_observe", "mcov_percent_covered", "mcov_launch_count", "mcov_replay_push",
            "mcov_replay_gather", "mcov_sim_step", "mcov_render_shape", "mcov_render")
@@ -79,6 +79,7 @@ def _declare(lib):
     lib.mcov_destroy.argtypes = [vp]
     lib.mcov_set_lidar_beams.argtypes = [vp, C.POINTER(C.c_double), i32]
     lib.mcov_pack_maps.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, vp]
+    lib.mcov_gen_maps.argtypes = [i32, i32, i32, i32, C.c_double, u64, vp, vp, vp, vp]
     lib.mcov_set_maps.argtypes = [vp, vp, vp, vp, i32, i32, i32]
     lib.mcov_state_layout.argtypes = [vp, C.POINTER(McovLayout)]
     lib.mcov_bind_state.argtypes = [vp, vp, C.c_size_t, vp]

@@ -68,6 +68,45 @@ __global__ void pack_maps_kernel(const int8_t* __restrict__ cells, int n_maps, i
     }
 }
 
+// gridgen on the device: same word loop as the packer, the cell value drawn instead of read.  Cell (m, xi, yi)
+// takes lane yi & 3 of Philox(counter = (m, xi, yi >> 2, tag), key = seed): independent of n_maps and layout.
+__global__ void gen_maps_kernel(int n_maps, int W, int L, int b, int strips, int Wp, unsigned long long thresh,
+                                uint2 key, uint32_t* __restrict__ wall, uint32_t* __restrict__ pos) {
+    const int PW = strips * Wp;
+    const long long total = (long long)n_maps * PW;
+    const int Wo = W + 2 * b, Lo = L + 2 * b;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int m = (int)(t / PW);
+        const int w = (int)(t % PW);
+        const int s = w / Wp, x = w % Wp;
+        uint32_t wb = 0, pb = 0;
+        if (x < Wo) {
+            const int xi = x - b;
+            int have = -1;                                            // yi >> 2 of the draw held in r
+            uint4 r = make_uint4(0u, 0u, 0u, 0u);
+            for (int k = 0; k < 32; ++k) {
+                const int y = s * 32 + k;
+                if (y >= Lo) break;
+                const int yi = y - b;
+                bool obst = true;                                     // border ring
+                if (xi >= 0 && xi < W && yi >= 0 && yi < L) {
+                    if ((yi >> 2) != have) {
+                        have = yi >> 2;
+                        r = mcov::philox4x32_10(make_uint4((uint32_t)m, (uint32_t)xi, (uint32_t)have, 0x47454E4Du), key);
+                    }
+                    const uint32_t u = (yi & 3) == 0 ? r.x : (yi & 3) == 1 ? r.y : (yi & 3) == 2 ? r.z : r.w;
+                    obst = (unsigned long long)u < thresh;
+                }
+                wb |= (uint32_t)obst << k;
+                pb |= (uint32_t)(!obst) << k;
+            }
+        }
+        wall[t] = wb;
+        pos[t] = pb;
+    }
+}
+
 __global__ void count_free_kernel(const uint32_t* __restrict__ pos, int n_maps, int PW, int32_t* out) {
     __shared__ int red[32];
     const int m = blockIdx.x;
@@ -317,6 +356,30 @@ int mcov_pack_maps(const int8_t* cells_dev, int n_maps, int W, int L, int add_bo
     count_free_kernel<<<n_maps, 256, 0, st>>>(pos_out_dev, n_maps, g.PW, free_counts_out_dev);
     cudaError_t ce = cudaGetLastError();
     if (ce != cudaSuccess) return cuda_fail(ce, "pack_maps launch");
+    return MCOV_OK;
+}
+
+int mcov_gen_maps(int n_maps, int W, int L, int add_border, double prob_obst, uint64_t seed,
+                  uint32_t* wall_out_dev, uint32_t* pos_out_dev, int32_t* free_counts_out_dev, void* stream) {
+    if (!wall_out_dev || !pos_out_dev || !free_counts_out_dev)
+        return fail(MCOV_ERR_NULL, "mcov_gen_maps: NULL buffer");
+    if (n_maps < 1 || W < 1 || L < 1) return fail(MCOV_ERR_BAD_CONFIG, "n_maps/W/L %d/%d/%d", n_maps, W, L);
+    if (!(prob_obst >= 0.0 && prob_obst <= 1.0))
+        return fail(MCOV_ERR_BAD_CONFIG, "prob_obst %g outside [0, 1]", prob_obst);
+    const int b = add_border ? 1 : 0;
+    const mcov::Geometry g = mcov::make_geometry(W + 2 * b, L + 2 * b);
+    if (g.W > 32767 || g.L > 32767) return fail(MCOV_ERR_BAD_CONFIG, "map larger than int16 coordinates");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long total = (long long)n_maps * g.PW;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    // a cell is an obstacle iff its 32-bit draw < prob_obst * 2^32 (exact for p = 0 and p = 1)
+    const unsigned long long thresh = (unsigned long long)llround(prob_obst * 4294967296.0);
+    gen_maps_kernel<<<grid, 256, 0, st>>>(n_maps, W, L, b, g.strips, g.Wp, thresh,
+                                          make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), wall_out_dev, pos_out_dev);
+    count_free_kernel<<<n_maps, 256, 0, st>>>(pos_out_dev, n_maps, g.PW, free_counts_out_dev);
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) return cuda_fail(ce, "gen_maps launch");
     return MCOV_OK;
 }
 

@@ -118,16 +118,52 @@ class MapTable:
         lib = _lib.load()
         cells = grids_to_cells(grids)
         M, W, L = cells.shape
-        b = 1 if add_border else 0
-        self.n_maps, self.W, self.L = M, W + 2 * b, L + 2 * b
-        self.strips, self.Wp, self.plane_words = _lib.plane_geometry(self.W, self.L)
-        self.device = torch.device(device)
+        self._alloc(M, W, L, add_border, device)
         with torch.cuda.device(self.device):
             cells_dev = torch.from_numpy(cells).to(self.device)
-            self.wall = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
-            self.pos = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
-            self.free_counts = torch.empty((M,), dtype=torch.int32, device=self.device)
+            b = 1 if add_border else 0
             st = torch.cuda.current_stream(self.device).cuda_stream
             _lib.check(lib.mcov_pack_maps(cells_dev.data_ptr(), M, W, L, b, self.wall.data_ptr(),
                                           self.pos.data_ptr(), self.free_counts.data_ptr(), st))
             torch.cuda.current_stream(self.device).synchronize()   # cells_dev may be freed now
+
+    def _alloc(self, M, W, L, add_border, device):
+        import torch
+        b = 1 if add_border else 0
+        self.add_border = bool(add_border)
+        self.n_maps, self.W, self.L = M, W + 2 * b, L + 2 * b
+        self.strips, self.Wp, self.plane_words = _lib.plane_geometry(self.W, self.L)
+        self.device = torch.device(device)
+        with torch.cuda.device(self.device):
+            self.wall = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
+            self.pos = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
+            self.free_counts = torch.empty((M,), dtype=torch.int32, device=self.device)
+
+    @classmethod
+    def generate(cls, grid_config, add_border, device="cuda:0", seed=0):
+        """``gridgen`` on the device (Utils/gridmaker.py:107-139): ``numgrids`` Bernoulli(prob_obst) maps of
+        gridwidth x gridlen written straight into the packed planes by ``mcov_gen_maps`` (Philox stream keyed
+        by ``seed``; same distribution as the reference, not numpy's draws).  The env constructors take the
+        table in place of a list of grids; ``add_border`` must be True for DecGridRL, False for SuperGridRL."""
+        import torch
+        lib = _lib.load()
+        self = cls.__new__(cls)
+        M, W, L = int(grid_config["numgrids"]), int(grid_config["gridwidth"]), int(grid_config["gridlen"])
+        self._alloc(M, W, L, add_border, device)
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            _lib.check(lib.mcov_gen_maps(M, W, L, 1 if add_border else 0, float(grid_config["prob_obst"]),
+                                         int(seed) & 0xFFFFFFFFFFFFFFFF, self.wall.data_ptr(), self.pos.data_ptr(),
+                                         self.free_counts.data_ptr(), st))
+        return self
+
+    def to_grids(self):
+        """The table back as the reference's host grids (float64 +1 free / -1 obstacle / 0 walkable-uncounted,
+        border ring removed): what ``gridgen`` would have returned for these maps."""
+        wall = unpack_plane_host(self.wall.cpu().numpy().view(np.uint32), self.W, self.L)
+        pos = unpack_plane_host(self.pos.cpu().numpy().view(np.uint32), self.W, self.L)
+        b = 1 if self.add_border else 0
+        g = np.where(wall, -1.0, np.where(pos, 1.0, 0.0))
+        if b:
+            g = g[:, 1:-1, 1:-1]
+        return [np.array(m) for m in g]

@@ -45,7 +45,13 @@ class _VecEnv:
         with torch.cuda.device(self.device):
             _lib.check(self._lib.mcov_create(C.byref(cfg), C.byref(self._handle)))
             self._post_create(env_config)
-            self.maps = MapTable(grids, add_border=(self.ENV_TYPE == _lib.ENV_DEC), device=self.device)
+            if isinstance(grids, MapTable):                       # a table built on the device (MapTable.generate)
+                if grids.add_border != (self.ENV_TYPE == _lib.ENV_DEC) or grids.device != self.device:
+                    raise ValueError("MapTable was built with add_border=%s on %s; this env needs add_border=%s on %s"
+                                     % (grids.add_border, grids.device, self.ENV_TYPE == _lib.ENV_DEC, self.device))
+                self.maps = grids
+            else:
+                self.maps = MapTable(grids, add_border=(self.ENV_TYPE == _lib.ENV_DEC), device=self.device)
             _lib.check(self._lib.mcov_set_maps(self._handle, self.maps.wall.data_ptr(),
                                                self.maps.pos.data_ptr(), self.maps.free_counts.data_ptr(),
                                                self.maps.n_maps, self.maps.W, self.maps.L))
