@@ -84,3 +84,16 @@ def test_env_on_a_generated_table_matches_the_oracle_on_its_grids():
         VecSuperGridRL(table, dict(numrobot=1, train_maxsteps=10, test_maxsteps=10, collision_penalty=5,
                                    senseradius=2, free_penalty=0, done_thresh=1, done_incr=0, terminal_reward=30,
                                    dist_reward=0, use_scanning=0), num_envs=2)      # bordered table, Super env
+
+
+@pytest.mark.parametrize("border", [False, True])
+@pytest.mark.parametrize("seed", [0, 3, (7 << 32) | 1])
+def test_generated_maps_equal_the_numpy_model(border, seed):
+    """Bit-exact pin of the kernel's draws: oracle/philox.py restates Philox4x32-10 (checked on CPU against the
+    published known-answer vectors) and the generator's counter / threshold rule."""
+    from marl_coverage_b200 import MapTable
+    from oracle.philox import gen_maps
+    cfg = dict(numgrids=5, gridwidth=33, gridlen=45, prob_obst=0.3)
+    got = MapTable.generate(cfg, add_border=border, seed=seed).to_grids()
+    want = gen_maps(5, 33, 45, 0.3, seed)
+    assert all(np.array_equal(a, b) for a, b in zip(got, want))
