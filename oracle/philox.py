@@ -46,3 +46,44 @@ def gen_maps(n_maps, W, L, prob_obst, seed):
     draws = philox4x32_10(ctr, key).reshape(n_maps, W, -1)[:, :, :L]          # [m, x, y]: lane y & 3 of group y >> 2
     grids = np.where(draws.astype(np.uint64) < np.uint64(thresh), -1.0, 1.0)
     return [np.array(g) for g in grids]
+
+
+RESET_TAG = 0x4D434F56
+
+
+def _bounded(u, n):
+    return (int(u) * int(n)) >> 32
+
+
+def draw_starts(walls, n_robots, seed, gid, episode):
+    """Restates ``draw_starts`` (mcov_common.cuh): the episode-start draw of the fused kernels for the env with
+    GLOBAL id ``gid`` at its ``episode``-th reset.  walls: bool [M, W, L] obstacle planes in env coordinates
+    (DecGridRL: with the border ring).  Returns (map index, int [N, 2] distinct walkable cells).
+    Same distribution as the reference's draws (dec_grid_rl.py:462-502, super_grid_rl.py:354-388): a uniform
+    map, then uniform cells by rejection; Philox counter = (gid, episode, draw number)."""
+    key = np.array([seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF], dtype=np.uint32)
+
+    def draw(k):
+        return philox4x32_10(np.array([gid, episode, k, RESET_TAG], dtype=np.uint32), key)
+
+    M, W, L = walls.shape
+    mi = _bounded(draw(0)[0], M)
+    wall = walls[mi]
+    cells = []
+    k = 1
+    while len(cells) < n_robots and k < 8192:
+        r = draw(k)
+        for h in range(2):
+            if len(cells) == n_robots:
+                break
+            x, y = _bounded(r[2 * h], W), _bounded(r[2 * h + 1], L)
+            if not wall[x, y] and (x, y) not in cells:
+                cells.append((x, y))
+        k += 1
+    for x in range(W):                                  # pathological maps: deterministic scan
+        for y in range(L):
+            if len(cells) < n_robots and not wall[x, y] and (x, y) not in cells:
+                cells.append((x, y))
+    while len(cells) < n_robots:
+        cells.append((0, 0))
+    return mi, np.array(cells, dtype=np.int64)

@@ -32,3 +32,24 @@ def test_gen_maps_model_properties():
     assert (gen_maps(2, 9, 9, 0.0, seed=1)[1] > 0).all() and (gen_maps(2, 9, 9, 1.0, seed=1)[1] < 0).all()
     hi = gen_maps(1, 5, 8, 0.5, seed=(7 << 32) | 1)[0]
     assert not np.array_equal(hi, gen_maps(1, 5, 8, 0.5, seed=1)[0])      # the high seed word is part of the key
+
+
+def test_draw_starts_model_properties():
+    from oracle.philox import draw_starts
+    rng = np.random.RandomState(1)
+    walls = rng.random_sample((5, 12, 9)) < 0.3
+    seen_maps = set()
+    for gid in range(40):
+        mi, cells = draw_starts(walls, 4, seed=77, gid=gid, episode=0)
+        seen_maps.add(mi)
+        assert cells.shape == (4, 2) and len({tuple(c) for c in cells}) == 4          # distinct
+        assert not walls[mi][cells[:, 0], cells[:, 1]].any()                          # walkable
+        again = draw_starts(walls, 4, seed=77, gid=gid, episode=0)
+        assert again[0] == mi and np.array_equal(again[1], cells)                     # a pure function of its key
+        assert not np.array_equal(draw_starts(walls, 4, seed=77, gid=gid, episode=1)[1], cells) or \
+            not np.array_equal(draw_starts(walls, 4, seed=78, gid=gid, episode=0)[1], cells)
+    assert len(seen_maps) == 5                                                        # every map is drawn
+    tight = np.ones((1, 4, 4), bool)
+    tight[0, 2, 1] = tight[0, 3, 3] = False                                           # two walkable cells, three robots
+    mi, cells = draw_starts(tight, 3, seed=1, gid=0, episode=0)
+    assert {tuple(c) for c in cells[:2]} == {(2, 1), (3, 3)} and tuple(cells[2]) == (0, 0)

@@ -97,3 +97,33 @@ def test_generated_maps_equal_the_numpy_model(border, seed):
     got = MapTable.generate(cfg, add_border=border, seed=seed).to_grids()
     want = gen_maps(5, 33, 45, 0.3, seed)
     assert all(np.array_equal(a, b) for a, b in zip(got, want))
+
+
+@pytest.mark.parametrize("kind", ["dec", "super"])
+def test_reset_draws_equal_the_numpy_model(kind):
+    """The episode-start draws of the fused kernels (map index, distinct walkable start cells) are a pure function
+    of (seed, GLOBAL env id, episode): oracle/philox.py:draw_starts restates them bit for bit."""
+    from marl_coverage_b200 import VecDecGridRL, VecSuperGridRL, load_grid_set
+    from oracle.philox import draw_starts
+    grids = load_grid_set("bg2_100x100", 5)
+    E, N, base = 48, 4, 1000
+    if kind == "dec":
+        cfg = dict(numrobot=N, maxsteps=1000, collision_penalty=5, done_thresh=1, done_incr=0, terminal_reward=30,
+                   dist_reward=0, train_maxsteps=1000, test_maxsteps=1000, egoradius=5, mini_map_rad=0,
+                   comm_radius=0, allow_comm=0, map_sharing=0, single_square_tool=0, dijkstra_input=0,
+                   sensor_type="square_sensor", sensor_config={"range": 2})
+        env = VecDecGridRL(grids, cfg, num_envs=E, env_id_base=base)
+        walls = np.stack([np.pad(g < 0, 1, constant_values=True) for g in grids])      # env coordinates: with the ring
+    else:
+        cfg = dict(numrobot=N, train_maxsteps=1000, test_maxsteps=1000, collision_penalty=5, senseradius=2,
+                   free_penalty=0, done_thresh=1, done_incr=0, terminal_reward=30, dist_reward=0, use_scanning=0)
+        env = VecSuperGridRL(grids, cfg, num_envs=E, env_id_base=base)
+        walls = np.stack([g < 0 for g in grids])
+    for episode, seed in enumerate([12345, (9 << 32) | 6]):
+        env.reset(seed=seed)
+        got_map = env.head()["map_idx"].cpu().numpy()
+        got_pos = env.positions().cpu().numpy()
+        for e in range(E):
+            mi, cells = draw_starts(walls, N, seed=seed, gid=base + e, episode=episode)
+            assert int(got_map[e]) == mi, (episode, e)
+            assert np.array_equal(got_pos[e].astype(np.int64), cells), (episode, e)
