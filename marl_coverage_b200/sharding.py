@@ -39,7 +39,7 @@ class StatsReducer:
     exposes the per-step global rows of the block that completed last, ``total`` their running sum.
     CPU / gloo: a plain blocking all-reduce with the same block semantics."""
 
-    def __init__(self, device, world=None, group=None, block=1):
+    def __init__(self, device, world=None, group=None, block=1, on_reduced=None, warm=True):
         import torch
         import torch.distributed as dist
         self.torch, self.dist, self.group = torch, dist, group
@@ -52,10 +52,33 @@ class StatsReducer:
         self.k = 0
         self._last = None
         self.overlap = self.cuda and self.world > 1
+        # on_reduced(view, first_step): called right after a block's reduction has been enqueued, inside the
+        # stream that ran it (side stream when overlapping) — e.g. to copy the global rows to pinned host memory
+        self.on_reduced = on_reduced
         if self.overlap:
             self.side = torch.cuda.Stream(device=self.device)
             self.ev_ready = [torch.cuda.Event() for _ in range(2)]
             self.ev_done = [torch.cuda.Event() for _ in range(2)]
+        if warm:
+            self.warm()
+
+    def warm(self):
+        """Runs one reduction of an all-zero block through every code path a real one takes (the collective on
+        the side stream, the row sum, the accumulation), so that the first real reduction — which lands in the
+        middle of a rollout — carries no one-off cost: lazy module loads of the two torch kernels, the first
+        NCCL launch on a brand-new stream.  Collective: every rank constructs its reducer at the same point."""
+        hook, self.on_reduced = self.on_reduced, None
+        for blk in (0, 1):
+            self._reduce(blk, self.block)
+            if self.block > 1:
+                self._reduce(blk, 1)
+        if self.overlap:
+            self.torch.cuda.current_stream(self.device).wait_stream(self.side)
+        if self.cuda:
+            self.torch.cuda.synchronize(self.device)
+        self.total.zero_()
+        self._last = None
+        self.on_reduced = hook
 
     def buffer(self):
         """The 8-double row the next step must write (waits until the block's previous reduction is done)."""
@@ -73,11 +96,15 @@ class StatsReducer:
                 self.side.wait_event(self.ev_ready[blk])
                 self.dist.all_reduce(view, group=self.group)
                 self.total.add_(view[0] if rows == 1 else view.sum(dim=0))
+                if self.on_reduced is not None:
+                    self.on_reduced(view, self.k - rows)
                 self.ev_done[blk].record(self.side)
         else:
             if self.world > 1:
                 self.dist.all_reduce(view, group=self.group)
             self.total.add_(view[0] if rows == 1 else view.sum(dim=0))
+            if self.on_reduced is not None:
+                self.on_reduced(view, self.k - rows)
         self._last = view
 
     def submit(self):

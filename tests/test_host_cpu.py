@@ -81,8 +81,12 @@ def test_reference_arm_prints_the_contract_line():
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    res = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "120",
-                          "--warmup", "0"], capture_output=True, text=True, timeout=300, cwd=root)
+    import time
+    t0 = time.perf_counter()
+    res = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "3",
+                          "--warmup", "1", "--sample-seconds", "1.0"], capture_output=True, text=True, timeout=300,
+                         cwd=root)
+    wall = time.perf_counter() - t0
     assert res.returncode == 0, res.stderr[-2000:]
     lines = [ln for ln in res.stdout.splitlines() if ln.startswith("{")]
     assert len(lines) == 1
@@ -98,3 +102,20 @@ def test_reference_arm_prints_the_contract_line():
     assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert "workload" in d["config"] and "model" not in d["config"]
+    # the arm runs exactly the samples it claims, and they fit in the run the driver clocks around it
+    assert d["steps"] == 3 and d["warmup"] == 1
+    assert 1000.0 <= d["ms_per_step"] < 2500.0 and d["ms_per_step"] * d["steps"] / 1e3 < wall
+    # same `config` object as the GPU arm prints for this workload
+    import bench
+    assert d["config"] == bench.config_dict("c5", bench.WORKLOADS["c5"][2], 1)[0]
+
+
+def test_bench_config_and_working_set_model():
+    import bench
+    cfg, flushed = bench.config_dict("c5", 131072, 1)
+    assert not flushed and cfg["obs_shape"] == [131072, 4, 3, 11, 11] and cfg["maps"].endswith("first 37 sorted")
+    assert bench.config_dict("c2", 4096, 1)[1] and bench.config_dict("c4", 256, 1)[1]        # L2-sized: flushed
+    assert not bench.config_dict("c3", 16384, 1)[1] and not bench.config_dict("super", 8192, 1)[1]
+    assert bench.config_dict("c5", 131072, 8)[0]["stats_allreduce"].startswith("NCCL")
+    assert bench.obs_shape_of("dec", dict(bench.C2_CFG, dijkstra_input=1), 7, 102, 102) == [7, 4, 4, 11, 11]
+    assert bench.obs_shape_of("super", bench.WORKLOADS["super"][3], 5, 100, 100) == [5, 7, 100, 100]

@@ -41,7 +41,8 @@ def _worker(rank, world, port, total_envs, steps, out_dir, block):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     lo, hi = shard_range(total_envs, rank, world)
-    red = StatsReducer("cpu", world=world, block=block)
+    rows = []
+    red = StatsReducer("cpu", world=world, block=block, on_reduced=lambda view, first: rows.append((first, view.clone())))
     rng = np.random.default_rng(0)                     # same stream on every rank: global per-env stats
     for _ in range(steps):
         per_env = rng.integers(0, 5, size=(total_envs, 8)).astype(np.float64)
@@ -50,6 +51,8 @@ def _worker(rank, world, port, total_envs, steps, out_dir, block):
         red.submit()
     tot = red.finish()
     np.save(os.path.join(out_dir, "tot_%d.npy" % rank), np.array(list(tot.values())))
+    # the hook saw every step's GLOBAL row exactly once, in order (warm-up reductions do not reach it)
+    np.save(os.path.join(out_dir, "rows_%d.npy" % rank), torch.cat([v for _, v in rows]).numpy())
     dist.destroy_process_group()
 
 
@@ -60,8 +63,11 @@ def test_stats_allreduce_gloo_world2(tmp_path, block):
              join=True)
     rng = np.random.default_rng(0)
     want = np.zeros(8)
+    per_step = []
     for _ in range(steps):
-        want += rng.integers(0, 5, size=(total_envs, 8)).astype(np.float64).sum(axis=0)
+        per_step.append(rng.integers(0, 5, size=(total_envs, 8)).astype(np.float64).sum(axis=0))
+        want += per_step[-1]
     for r in range(world):
         got = np.load(os.path.join(str(tmp_path), "tot_%d.npy" % r))
         assert np.array_equal(got, want)               # every rank holds the global sums
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), "rows_%d.npy" % r)), np.stack(per_step))
