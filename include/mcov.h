@@ -19,7 +19,10 @@
  *   - the library owns only the opaque handle.  Simulator state lives in a caller-owned arena
  *     (mcov_state_bytes / mcov_bind_state) whose layout is reported by mcov_state_layout so the
  *     host side can view/patch any field (get_state / set_state) without further entry points;
- *   - one handle <-> one device; calls on one handle must be serialised by the caller.
+ *   - one handle <-> one device (the one current at mcov_create; a call with another device current returns
+ *     MCOV_ERR_STATE); calls on one handle must be serialised by the caller;
+ *   - values read from caller-supplied DEVICE buffers that become addresses (map indices, start poses, replay
+ *     sample indices) are clamped into range by the kernels; they are never trusted.
  *
  * Bit-plane layout ("strip-major"): a W x L boolean plane is stored as 32-bit words,
  *   word index = strip * Wp + x,   bit b of that word = cell (x, y = 32*strip + b),
@@ -37,11 +40,14 @@
 extern "C" {
 #endif
 
-#define MCOV_ABI_VERSION 6
+#define MCOV_ABI_VERSION 7
 #define MCOV_MAX_ROBOTS 32       /* base-4 joint actions live in an int64: 31 digits; lanes: 32 */
 #define MCOV_MAX_RADIUS 15       /* sensor range, egoradius, mini_map_rad: windows fit 32 bits  */
 #define MCOV_MAX_LASERS 1024
 #define MCOV_STATS_LEN 8
+/* done_out bits of mcov_step */
+#define MCOV_DONE_TERMINAL 1     /* the reference's done(): coverage threshold reached / Dec maxsteps / sentinel */
+#define MCOV_DONE_TRUNCATED 2    /* episode cut at truncate_steps (generate_episode's done = True, utils.py:25-31) */
 
 typedef struct mcov_env mcov_env; /* opaque */
 
@@ -158,6 +164,13 @@ int mcov_gen_maps(int n_maps, int W, int L, int add_border, double prob_obst, ui
 int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_dev,
                   const int32_t* free_counts_dev, int n_maps, int W, int L);
 
+/* Per-cell reward of covering a free cell for SuperGridRL (super_grid_rl.py:189 `reward += self._grid[j][k]`,
+ * sim_env.py:159): float64 [n_maps][W][L] in map coordinates, kept by reference; NULL (the default after every
+ * mcov_set_maps) = every free cell is worth 1.0, which is what the +-1 PNG maps give.  The sign planes of
+ * mcov_pack_maps still decide obstacle / walkable / counted.  DecGridRL handles are refused: its reward is the
+ * count of newly visited cells (dec_grid_rl.py:243-256) and never reads a cell's value. */
+int mcov_set_cell_values(mcov_env* env, const double* values_dev);
+
 /* State arena: size/layout after mcov_set_maps; the caller allocates (256-byte aligned) and binds. */
 int mcov_state_layout(const mcov_env* env, mcov_layout* out);
 int mcov_bind_state(mcov_env* env, void* arena_dev, size_t bytes, void* stream);
@@ -176,7 +189,11 @@ int mcov_reset(mcov_env* env, const uint8_t* mask_dev, const int32_t* map_idx_de
  * envs: moves with collision checks, sensing, reward, termination, observation.
  *   obs_out_dev     float32, shape mcov_obs_shape, 16-byte aligned
  *   reward_out_dev  float32 [E];  reward64_out_dev float64 [E] or NULL (reference precision)
- *   done_out_dev    uint8 [E]
+ *   done_out_dev    uint8 [E]: bit 0 (MCOV_DONE_TERMINAL) = the reference's done flag; bit 1
+ *                   (MCOV_DONE_TRUNCATED) = the episode was cut at truncate_steps this step.  With auto_reset
+ *                   the env restarts in place in the same call and obs_out holds the NEW episode's first
+ *                   observation: a non-zero done byte is the only sign of the episode boundary, so a
+ *                   learner must treat any non-zero value as "do not bootstrap across this step"
  *   stats_out_dev   float64 [MCOV_STATS_LEN] or NULL: this step's sums over the E envs of
  *                   {episodes finished, their returns, their lengths, their final coverage,
  *                    collisions, newly covered cells, agent-steps, 0}                            */
@@ -206,8 +223,9 @@ int mcov_replay_push(const float* state_dev, const float* next_state_dev, int ro
                      float* ring_next_dev, float* ring_action_dev, float* ring_reward_dev,
                      float* ring_done_dev, int64_t ptr, int64_t capacity, void* stream);
 
-/* ReplayBuffer.samplebatch gather, Policies/replaybuffer.py:66-72: out_*[b] = ring_*[idx[b]]. */
-int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int act_dim,
+/* ReplayBuffer.samplebatch gather, Policies/replaybuffer.py:66-72: out_*[b] = ring_*[idx[b]]; indices are
+ * clamped to [0, capacity) on the device. */
+int mcov_replay_gather(const int64_t* idx_dev, int64_t capacity, int batch, int row_floats, int act_dim,
                        const float* ring_state_dev, const float* ring_next_dev, const float* ring_action_dev,
                        const float* ring_reward_dev, const float* ring_done_dev, float* out_state_dev,
                        float* out_next_dev, float* out_action_dev, float* out_reward_dev, float* out_done_dev,

@@ -55,11 +55,13 @@ def build(force=False, verbose=False):
             raise RuntimeError("nvcc failed building libmcov_b200.so")
         if verbose:
             sys.stderr.write(res.stderr)
+    tmp = LIB + ".tmp.%d" % os.getpid()                        # link aside, then rename: the library is never half-written
     res = subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC"] +
-                         [obj for obj, _ in results] + ["-o", LIB], capture_output=True, text=True)
+                         [obj for obj, _ in results] + ["-o", tmp], capture_output=True, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
         raise RuntimeError("nvcc failed linking libmcov_b200.so")
+    os.replace(tmp, LIB)
     return LIB
 
 

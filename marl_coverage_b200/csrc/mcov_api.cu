@@ -137,11 +137,28 @@ unsigned char* scratch_super_dt(const mcov_env* env) {
 }
 unsigned char* scratch_extras(const mcov_env* env) { return scratch_super_dt(env); }   // Dec: same slot
 
+// one handle <-> one device: its buffers, map table and kernel attributes belong to the device that was current
+// at mcov_create, so a call with another device current is refused instead of launching there
+int check_device(const mcov_env* env) {
+    int dev = -1;
+    cudaError_t ce = cudaGetDevice(&dev);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaGetDevice");
+    if (dev != env->device)
+        return fail(MCOV_ERR_STATE, "handle was created on device %d, the current device is %d", env->device, dev);
+    return MCOV_OK;
+}
+
+int sm_count() {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms > 0 ? sms : 148;
+}
+
 int check_ready(const mcov_env* env) {
     if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
     if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
     if (!env->bound) return fail(MCOV_ERR_STATE, "mcov_bind_state has not been called");
-    return MCOV_OK;
+    return check_device(env);
 }
 
 void fill_dec_params(mcov_env* env, mcov::DecParams& p) {
@@ -207,6 +224,7 @@ void fill_super_params(mcov_env* env, mcov::SuperParams& p) {
     p.wall = env->wall;
     p.pos = env->pos;
     p.free_counts = env->free_counts;
+    p.cell_values = env->cell_values;
     p.n_maps = env->n_maps;
     p.hdr = env->arena + l.off_hdr;
     p.hdr_stride = l.hdr_stride;
@@ -273,6 +291,7 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
     ce = cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, e->device);
     if (ce != cudaSuccess) { delete e; return cuda_fail(ce, "cudaDeviceGetAttribute"); }
     e->obs_C = obs_channels(c);
+    e->debug = getenv("MCOV_DEBUG") ? atoi(getenv("MCOV_DEBUG")) : 0;
     *out = e;
     return MCOV_OK;
 }
@@ -351,7 +370,7 @@ int mcov_pack_maps(const int8_t* cells_dev, int n_maps, int W, int L, int add_bo
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const long long total = (long long)n_maps * g.PW;
     int grid = (int)((total + 255) / 256);
-    if (grid > 148 * 16) grid = 148 * 16;
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
     pack_maps_kernel<<<grid, 256, 0, st>>>(cells_dev, n_maps, W, L, b, g.strips, g.Wp, wall_out_dev, pos_out_dev);
     count_free_kernel<<<n_maps, 256, 0, st>>>(pos_out_dev, n_maps, g.PW, free_counts_out_dev);
     cudaError_t ce = cudaGetLastError();
@@ -372,7 +391,7 @@ int mcov_gen_maps(int n_maps, int W, int L, int add_border, double prob_obst, ui
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const long long total = (long long)n_maps * g.PW;
     int grid = (int)((total + 255) / 256);
-    if (grid > 148 * 16) grid = 148 * 16;
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
     // a cell is an obstacle iff its 32-bit draw < prob_obst * 2^32 (exact for p = 0 and p = 1)
     const unsigned long long thresh = (unsigned long long)llround(prob_obst * 4294967296.0);
     gen_maps_kernel<<<grid, 256, 0, st>>>(n_maps, W, L, b, g.strips, g.Wp, thresh,
@@ -405,6 +424,7 @@ int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_d
     env->n_maps = n_maps;
     env->maps_set = true;
     env->bound = false;
+    env->cell_values = nullptr;                                   // belongs to the previous table
 
     // ---- arena layout ---------------------------------------------------------------------------
     const mcov_config& c = env->cfg;
@@ -440,6 +460,17 @@ int mcov_set_maps(mcov_env* env, const uint32_t* wall_dev, const uint32_t* pos_d
     if (c.env_type == MCOV_ENV_SUPER) off = align_up64(off + mcov::super_dt_scratch_bytes(env), 256);
     else off = align_up64(off + mcov::dec_extras_scratch_bytes(env), 256);
     l.total_bytes = off;
+    return MCOV_OK;
+}
+
+int mcov_set_cell_values(mcov_env* env, const double* values_dev) {
+    if (!env) return fail(MCOV_ERR_NULL, "env handle is NULL");
+    if (env->cfg.env_type != MCOV_ENV_SUPER)
+        return fail(MCOV_ERR_BAD_CONFIG, "cell values only enter SuperGridRL's reward (super_grid_rl.py:189); "
+                    "DecGridRL's is a count (dec_grid_rl.py:243-256)");
+    if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
+    if (values_dev && !aligned(values_dev, 8)) return fail(MCOV_ERR_ALIGN, "cell values must be 8-byte aligned");
+    env->cell_values = values_dev;
     return MCOV_OK;
 }
 
@@ -666,7 +697,7 @@ int mcov_replay_push(const float* state_dev, const float* next_state_dev, int ro
     return MCOV_OK;
 }
 
-int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int act_dim,
+int mcov_replay_gather(const int64_t* idx_dev, int64_t capacity, int batch, int row_floats, int act_dim,
                        const float* ring_state_dev, const float* ring_next_dev, const float* ring_action_dev,
                        const float* ring_reward_dev, const float* ring_done_dev, float* out_state_dev,
                        float* out_next_dev, float* out_action_dev, float* out_reward_dev, float* out_done_dev,
@@ -674,10 +705,11 @@ int mcov_replay_gather(const int64_t* idx_dev, int batch, int row_floats, int ac
     if (!idx_dev || !ring_state_dev || !ring_next_dev || !ring_action_dev || !ring_reward_dev || !ring_done_dev ||
         !out_state_dev || !out_next_dev || !out_action_dev || !out_reward_dev || !out_done_dev)
         return fail(MCOV_ERR_NULL, "mcov_replay_gather: NULL buffer");
-    if (batch < 1 || row_floats < 1 || act_dim < 1)
-        return fail(MCOV_ERR_BAD_CONFIG, "mcov_replay_gather: batch %d row %d act_dim %d", batch, row_floats, act_dim);
+    if (batch < 1 || row_floats < 1 || act_dim < 1 || capacity < 1)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_replay_gather: batch %d row %d act_dim %d capacity %lld", batch,
+                    row_floats, act_dim, (long long)capacity);
     cudaError_t ce = mcov::launch_replay_gather(
-        reinterpret_cast<const long long*>(idx_dev), batch, row_floats, act_dim, ring_state_dev, ring_next_dev,
+        reinterpret_cast<const long long*>(idx_dev), (long long)capacity, batch, row_floats, act_dim, ring_state_dev, ring_next_dev,
         ring_action_dev, ring_reward_dev, ring_done_dev, out_state_dev, out_next_dev, out_action_dev, out_reward_dev,
         out_done_dev, static_cast<cudaStream_t>(stream));
     if (ce != cudaSuccess) return cuda_fail(ce, "replay gather launch");
@@ -693,6 +725,7 @@ int mcov_sim_step(mcov_env* env, const float* state_dev, const uint8_t* actions_
     if (!env->maps_set) return fail(MCOV_ERR_STATE, "mcov_set_maps has not been called");
     if (!state_dev || !actions_dev || !next_state_dev) return fail(MCOV_ERR_NULL, "mcov_sim_step: NULL buffer");
     if (batch < 1) return fail(MCOV_ERR_BAD_CONFIG, "mcov_sim_step: batch %d", batch);
+    if (int rc = check_device(env)) return rc;
     if (!aligned(state_dev, 4) || !aligned(next_state_dev, 4))
         return fail(MCOV_ERR_ALIGN, "mcov_sim_step: state buffers must be float aligned");
     const mcov_config& c = env->cfg;
@@ -709,6 +742,8 @@ int mcov_sim_step(mcov_env* env, const float* state_dev, const uint8_t* actions_
     p.wall = env->wall;
     p.pos = env->pos;
     p.free_counts = env->free_counts;
+    p.cell_values = env->cell_values;
+    p.n_maps = env->n_maps;
     p.state = state_dev;
     p.actions = actions_dev;
     p.map_idx = map_idx_dev;

@@ -51,13 +51,15 @@ __global__ void __launch_bounds__(SIM_THREADS, MCOV_SIM_MINB) sim_lookahead_kern
         const float* in = p.state + (size_t)b * 4 * cells;
         float* out = p.next_state + (size_t)b * 4 * cells;
         const bool inplace = (in == out);
-        const int mi = p.map_idx ? p.map_idx[b] : 0;
+        const int mi = p.map_idx ? min(max(p.map_idx[b], 0), p.n_maps - 1) : 0;       // device value: clamped
         const uint32_t* wall = p.wall + (size_t)mi * g.PW;
         const uint32_t* posm = p.pos + (size_t)mi * g.PW;
 
         // ---- stream the planes first (nothing below depends on the pose): out[0] = 0, out[1..3] = in[1..3];
         //      count covered cells and find the robot (np.nonzero(pos_img), sim_env.py:78) on the way -------
-        if (tid == 0) s_first = p.pos_xy ? (int)p.pos_xy[2 * b] * L + (int)p.pos_xy[2 * b + 1] : 0x7fffffff;
+        if (tid == 0)
+            s_first = p.pos_xy ? min(max((int)p.pos_xy[2 * b], 0), W - 1) * L + min(max((int)p.pos_xy[2 * b + 1], 0), L - 1)
+                               : 0x7fffffff;
         int covered = 0, first = 0x7fffffff;
         if (p.vec_ok) {
             const int q = cells >> 2;
@@ -150,7 +152,11 @@ __global__ void __launch_bounds__(SIM_THREADS, MCOV_SIM_MINB) sim_lookahead_kern
             int newly = 0;
             for (int k = 0; k < S * S; ++k) {
                 const int cls = s_cls[k];
-                if (cls == CELL_NEW) { r += (double)s_val[k]; ++newly; }
+                if (cls == CELL_NEW) {                       // reward += grid[j][k] (sim_env.py:159)
+                    r += p.cell_values ? __ldg(p.cell_values + ((size_t)mi * W + (px - p.R + k / S)) * L + (py - p.R + k % S))
+                                       : (double)s_val[k];
+                    ++newly;
+                }
                 else if (cls == CELL_AGAIN) r -= p.free_penalty;
             }
             if (inplace && s_first != 0x7fffffff) out[s_first] = 0.0f;

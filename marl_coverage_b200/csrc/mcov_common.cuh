@@ -117,7 +117,9 @@ __device__ inline void draw_starts(const uint32_t* __restrict__ wall_table, cons
     const uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
     int mi;
     if (map_idx_in) {
-        mi = map_idx_in[e];
+        // caller-supplied device values are clamped, never trusted as addresses (host-side numpy inputs are
+        // range-checked by the Python stub before they get here; a device tensor cannot be without a sync)
+        mi = min(max(map_idx_in[e], 0), n_maps - 1);
     } else {
         const uint4 r = philox4x32_10(make_uint4(gid, episode, 0u, 0x4D434F56u), key);
         mi = bounded(r.x, n_maps);
@@ -125,7 +127,8 @@ __device__ inline void draw_starts(const uint32_t* __restrict__ wall_table, cons
     *map_out = mi;
     if (start_xy_in) {
         const int16_t* s = start_xy_in + (size_t)e * N * 2;
-        for (int j = 0; j < N; ++j) posS[j] = pack_xy(s[2 * j], s[2 * j + 1]);
+        for (int j = 0; j < N; ++j)
+            posS[j] = pack_xy(min(max((int)s[2 * j], 0), g.W - 1), min(max((int)s[2 * j + 1], 0), g.L - 1));
         return;
     }
     const uint32_t* wall = wall_table + (size_t)mi * g.PW;

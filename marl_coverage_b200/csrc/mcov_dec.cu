@@ -605,6 +605,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
         if (lg == 0) {
             double r = 0.0;
             int dn = 0, nr = 0;
+            bool trunc = false;
             if (sentinel) {
                 dn = 1;                                            // dec_grid_rl.py:105-107
                 nr = 1;
@@ -624,7 +625,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 head->currstep = cs;
                 head->flags = shown;
                 head->ep_return = epr;
-                const bool trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
+                trunc = p.truncate_steps > 0 && cs >= p.truncate_steps;
                 sm.stats[4] += (double)ncoll;
                 sm.stats[5] += (double)cnt;
                 sm.stats[6] += (double)N;
@@ -638,7 +639,9 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             }
             p.reward[e] = (float)r;
             if (p.reward64) p.reward64[e] = r;
-            p.done[e] = (uint8_t)dn;
+            // bit 0: the reference's done(); bit 1: cut at truncate_steps (generate_episode's done = True,
+            // Utils/utils.py:25-31) — visible to the caller even when the fused auto-reset consumes the episode end
+            p.done[e] = (uint8_t)(dn | (trunc ? MCOV_DONE_TRUNCATED : 0));
             flag = nr && p.auto_reset;
             p.needs_reset[e] = (nr && !flag) ? 1 : 0;
         }
@@ -903,11 +906,17 @@ inline DecLaunchShape dec_shape(const mcov_env* env) {
 inline uint32_t magic_for(int d) { return (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); }
 
 template <class SP>
-cudaError_t launch_dec_t(const DecLaunchShape& s, const DecParams& p, cudaStream_t st) {
-    if (s.smem > 48 * 1024) {
+cudaError_t launch_dec_t(mcov_env* env, const DecLaunchShape& s, const DecParams& p, cudaStream_t st) {
+    // the opt-in is a per-device property of the kernel; a handle lives on one device and always launches the
+    // same instantiation with the same shape, so it is set once per handle (not per process: a second device
+    // in the same process needs its own call)
+    const void* fn = reinterpret_cast<const void*>(&dec_env_kernel<SP>);
+    if (s.smem > 48 * 1024 && (env->dec_smem_func != fn || env->dec_smem_configured < s.smem)) {
         cudaError_t err = cudaFuncSetAttribute(dec_env_kernel<SP>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
         if (err != cudaSuccess) return err;
+        env->dec_smem_func = fn;
+        env->dec_smem_configured = s.smem;
     }
     dec_env_kernel<SP><<<s.grid, s.threads, s.smem, st>>>(p);
     return cudaGetLastError();
@@ -928,8 +937,7 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.n_magic = magic_for(p.N);
     p.l_magic = magic_for(p.n_lasers > 0 ? p.n_lasers : 1);
     const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
-    static const int debug = getenv("MCOV_DEBUG") ? atoi(getenv("MCOV_DEBUG")) : 0;
-    p.debug = debug;
+    p.debug = env->debug;                                           // MCOV_DEBUG, read once at mcov_create
     if ((uint64_t)p.E * p.N * p.g.PW >= 0xffffffffull) return cudaErrorInvalidValue;   // 32-bit word offsets
     cudaError_t err;
     const bool plain = p.C == 3 && !p.single_tool && p.comm_radius == 0;
@@ -937,18 +945,18 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     const bool c2 = plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5;
     const bool c3 = plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5;
     const bool c4 = plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5;
-    if (c2 && s.G == 4) err = launch_dec_t<Spec<4, false, 4, 2, 5>>(s, p, st);
-    else if (s.G == 4) err = lidar ? launch_dec_t<Spec<4, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<4, false, 0, 0, 0>>(s, p, st);
-    else if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(s, p, st);
-    else if (c2 && s.G == 16) err = launch_dec_t<Spec<16, false, 4, 2, 5>>(s, p, st);
-    else if (c2 && s.G == 32) err = launch_dec_t<Spec<32, false, 4, 2, 5>>(s, p, st);
-    else if (c3 && s.G == 8) err = launch_dec_t<Spec<8, true, 8, 10, 5>>(s, p, st);
-    else if (c3 && s.G == 32) err = launch_dec_t<Spec<32, true, 8, 10, 5>>(s, p, st);
-    else if (c4 && s.G == 16) err = launch_dec_t<Spec<16, false, 16, 2, 5>>(s, p, st);
-    else if (c4 && s.G == 32) err = launch_dec_t<Spec<32, false, 16, 2, 5>>(s, p, st);
-    else if (s.G == 8) err = lidar ? launch_dec_t<Spec<8, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<8, false, 0, 0, 0>>(s, p, st);
-    else if (s.G == 16) err = lidar ? launch_dec_t<Spec<16, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<16, false, 0, 0, 0>>(s, p, st);
-    else err = lidar ? launch_dec_t<Spec<32, true, 0, 0, 0>>(s, p, st) : launch_dec_t<Spec<32, false, 0, 0, 0>>(s, p, st);
+    if (c2 && s.G == 4) err = launch_dec_t<Spec<4, false, 4, 2, 5>>(env, s, p, st);
+    else if (s.G == 4) err = lidar ? launch_dec_t<Spec<4, true, 0, 0, 0>>(env, s, p, st) : launch_dec_t<Spec<4, false, 0, 0, 0>>(env, s, p, st);
+    else if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(env, s, p, st);
+    else if (c2 && s.G == 16) err = launch_dec_t<Spec<16, false, 4, 2, 5>>(env, s, p, st);
+    else if (c2 && s.G == 32) err = launch_dec_t<Spec<32, false, 4, 2, 5>>(env, s, p, st);
+    else if (c3 && s.G == 8) err = launch_dec_t<Spec<8, true, 8, 10, 5>>(env, s, p, st);
+    else if (c3 && s.G == 32) err = launch_dec_t<Spec<32, true, 8, 10, 5>>(env, s, p, st);
+    else if (c4 && s.G == 16) err = launch_dec_t<Spec<16, false, 16, 2, 5>>(env, s, p, st);
+    else if (c4 && s.G == 32) err = launch_dec_t<Spec<32, false, 16, 2, 5>>(env, s, p, st);
+    else if (s.G == 8) err = lidar ? launch_dec_t<Spec<8, true, 0, 0, 0>>(env, s, p, st) : launch_dec_t<Spec<8, false, 0, 0, 0>>(env, s, p, st);
+    else if (s.G == 16) err = lidar ? launch_dec_t<Spec<16, true, 0, 0, 0>>(env, s, p, st) : launch_dec_t<Spec<16, false, 0, 0, 0>>(env, s, p, st);
+    else err = lidar ? launch_dec_t<Spec<32, true, 0, 0, 0>>(env, s, p, st) : launch_dec_t<Spec<32, false, 0, 0, 0>>(env, s, p, st);
     env->launches++;
     return err;
 }

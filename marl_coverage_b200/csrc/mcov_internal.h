@@ -78,6 +78,7 @@ struct SuperParams {
     const uint32_t* wall;
     const uint32_t* pos;
     const int32_t* free_counts;
+    const double* cell_values;  // [n_maps][W][L] reward of covering a cell (super_grid_rl.py:189), or null = 1.0
     int n_maps;
     unsigned char* hdr;
     int hdr_stride, off_pos, off_cov;
@@ -115,8 +116,10 @@ struct SimParams {
     const uint32_t* wall;
     const uint32_t* pos;
     const int32_t* free_counts;
+    const double* cell_values; // [n_maps][W][L] or null (sim_env.py:159 reward += grid[j][k])
     const float* state;        // [B][4][W][L]
     const uint8_t* actions;    // [B]
+    int n_maps;
     const int32_t* map_idx;    // [B] or null (map 0)
     const int16_t* pos_xy;     // [B][2] or null (scan the position plane)
     float* next_state;         // [B][4][W][L]; == state: patch in place
@@ -160,6 +163,10 @@ struct mcov_env {
     int64_t launches;
     uint64_t seed;            // seed of the last mcov_reset (auto-reset draws derive from it)
     int obs_C;
+    int debug;                // MCOV_DEBUG at mcov_create (profiling aids; 0 in normal use)
+    size_t dec_smem_configured, super_smem_configured;   // dynamic shared memory opted into on this handle's device
+    const void* dec_smem_func;  // ... and for which instantiation (MCOV_DEC_GROUP can change it between launches)
+    const double* cell_values;  // Super: float64 [n_maps][W][L] reward of covering a cell, or null (= 1.0)
 };
 
 // kernel launchers (defined in the .cu files)
@@ -178,7 +185,7 @@ cudaError_t launch_replay_push(const float* state, const float* next_state, int 
                                const uint8_t* act_u8, const float* act_f32, int act_dim, const float* reward,
                                const uint8_t* done, int E, float* r_state, float* r_next, float* r_action,
                                float* r_reward, float* r_done, long long ptr, long long capacity, cudaStream_t st);
-cudaError_t launch_replay_gather(const long long* idx, int B, int row_floats, int act_dim, const float* r_state,
+cudaError_t launch_replay_gather(const long long* idx, long long capacity, int B, int row_floats, int act_dim, const float* r_state,
                                  const float* r_next, const float* r_action, const float* r_reward,
                                  const float* r_done, float* o_state, float* o_next, float* o_action,
                                  float* o_reward, float* o_done, cudaStream_t st);

@@ -123,15 +123,17 @@ replay_push_kernel(const VT* __restrict__ state, const VT* __restrict__ next_sta
 
 template <class VT>
 __global__ void __launch_bounds__(256)
-replay_gather_kernel(const long long* __restrict__ idx, int B, int row, int act_dim,
+replay_gather_kernel(const long long* __restrict__ idx, long long capacity, int B, int row, int act_dim,
                      const VT* __restrict__ r_state, const VT* __restrict__ r_next,
                      const float* __restrict__ r_action, const float* __restrict__ r_reward,
                      const float* __restrict__ r_done, VT* __restrict__ o_state, VT* __restrict__ o_next,
                      float* __restrict__ o_action, float* __restrict__ o_reward, float* __restrict__ o_done) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const int lane = threadIdx.x & 31, nwarps = (int)(stride >> 5);
+    // sampled indices are device values nobody has looked at: clamped into the ring, never used raw
+    auto ring_row = [&](int b) { return min(max(idx[b], 0ll), capacity - 1); };
     for (int b = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5); b < B; b += nwarps) {
-        const long long src = idx[b] * row, dst = (long long)b * row;
+        const long long src = ring_row(b) * row, dst = (long long)b * row;
         if (MCOV_REPLAY_SHIFT && sizeof(VT) == 4 && row >= 16) {
             copy_row_shifted<false>(reinterpret_cast<const float*>(r_state + src), reinterpret_cast<float*>(o_state + dst), row, lane);
             copy_row_shifted<false>(reinterpret_cast<const float*>(r_next + src), reinterpret_cast<float*>(o_next + dst), row, lane);
@@ -150,11 +152,11 @@ replay_gather_kernel(const long long* __restrict__ idx, int B, int row, int act_
     const long long small = (long long)B * act_dim;
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < small; k += stride) {
         const int b = (int)(k / act_dim);
-        o_action[k] = r_action[idx[b] * act_dim + (k - (long long)b * act_dim)];
+        o_action[k] = r_action[ring_row(b) * act_dim + (k - (long long)b * act_dim)];
     }
     for (long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x; b < B; b += stride) {
-        o_reward[b] = r_reward[idx[b]];
-        o_done[b] = r_done[idx[b]];
+        o_reward[b] = r_reward[ring_row((int)b)];
+        o_done[b] = r_done[ring_row((int)b)];
     }
 }
 
@@ -196,7 +198,7 @@ cudaError_t launch_replay_push(const float* state, const float* next_state, int 
     return cudaGetLastError();
 }
 
-cudaError_t launch_replay_gather(const long long* idx, int B, int row_floats, int act_dim, const float* r_state,
+cudaError_t launch_replay_gather(const long long* idx, long long capacity, int B, int row_floats, int act_dim, const float* r_state,
                                  const float* r_next, const float* r_action, const float* r_reward,
                                  const float* r_done, float* o_state, float* o_next, float* o_action,
                                  float* o_reward, float* o_done, cudaStream_t st) {
@@ -204,12 +206,12 @@ cudaError_t launch_replay_gather(const long long* idx, int B, int row_floats, in
     if (vec) {
         const int row = row_floats / 4;
         replay_gather_kernel<float4><<<grid_for((long long)B * 32), 256, 0, st>>>(
-            idx, B, row, act_dim, reinterpret_cast<const float4*>(r_state), reinterpret_cast<const float4*>(r_next),
+            idx, capacity, B, row, act_dim, reinterpret_cast<const float4*>(r_state), reinterpret_cast<const float4*>(r_next),
             r_action, r_reward, r_done, reinterpret_cast<float4*>(o_state), reinterpret_cast<float4*>(o_next),
             o_action, o_reward, o_done);
     } else {
         replay_gather_kernel<float><<<grid_for((long long)B * 32), 256, 0, st>>>(
-            idx, B, row_floats, act_dim, r_state, r_next, r_action, r_reward, r_done, o_state, o_next, o_action,
+            idx, capacity, B, row_floats, act_dim, r_state, r_next, r_action, r_reward, r_done, o_state, o_next, o_action,
             o_reward, o_done);
     }
     return cudaGetLastError();

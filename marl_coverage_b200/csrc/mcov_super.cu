@@ -424,8 +424,15 @@ __device__ void super_dynamics(const SuperParams& p, SuperSmem& sm, EnvSlot& slo
                 while (both) {
                     const uint32_t bit = both & (0u - both);
                     both ^= bit;
-                    if (rb.x & bit) racc = __dadd_rn(racc, 1.0);                 // += grid[j][k]
-                    else racc = __dsub_rn(racc, p.free_penalty);                 // -= free_penalty
+                    if (rb.x & bit) {                                            // += grid[j][k]
+                        double v = 1.0;
+                        if (p.cell_values)
+                            v = __ldg(p.cell_values + ((size_t)map_idx * W + (unpack_x(pv) - R + r)) * L +
+                                      (unpack_y(pv) - R + (__ffs(bit) - 1)));
+                        racc = __dadd_rn(racc, v);
+                    } else {
+                        racc = __dsub_rn(racc, p.free_penalty);                 // -= free_penalty
+                    }
                 }
             }
             // motion_penalty quirk (:203-208): -1 per slot on the very first step
@@ -466,7 +473,7 @@ __device__ void super_dynamics(const SuperParams& p, SuperSmem& sm, EnvSlot& slo
             }
             p.reward[e] = (float)r;
             if (p.reward64) p.reward64[e] = r;
-            p.done[e] = (uint8_t)dn;
+            p.done[e] = (uint8_t)(dn | (trunc ? MCOV_DONE_TRUNCATED : 0));   // bit 1: cut at truncate_steps
             again = (nr && p.auto_reset) ? 1 : 0;
             p.needs_reset[e] = (nr && !p.auto_reset) ? 1 : 0;
         }
@@ -648,8 +655,7 @@ cudaError_t launch_super(mcov_env* env, SuperParams& p, cudaStream_t st) {
     p.dt_pitch = s.pitch;
     if (s.global_dt && !p.dt_scratch) return cudaErrorInvalidValue;
     if (!s.global_dt) p.dt_scratch = nullptr;
-    static size_t configured_smem = 0;                        // one process drives one device
-    if (s.smem > configured_smem) {
+    if (s.smem > env->super_smem_configured) {                // per handle = per device (see launch_dec_t)
         cudaError_t err = cudaSuccess;
         if (s.smem > 38 * 1024)
             err = cudaFuncSetAttribute(super_env_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem);
@@ -657,7 +663,7 @@ cudaError_t launch_super(mcov_env* env, SuperParams& p, cudaStream_t st) {
             err = cudaFuncSetAttribute(super_env_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                        (int)cudaSharedmemCarveoutMaxShared);
         if (err != cudaSuccess) return err;
-        configured_smem = s.smem;
+        env->super_smem_configured = s.smem;
     }
     super_env_kernel<<<s.grid, ST, s.smem, st>>>(p, s.cells);
     env->launches++;

@@ -69,13 +69,18 @@ def gridgen(grid_config):
 
 
 def grids_to_cells(grids):
-    """float grids -> int8 sign cells [M, W, L]; rejects maps the bit planes cannot represent."""
+    """float grids -> (int8 sign cells [M, W, L], float64 cell values [M, W, L] or None).
+
+    The bit planes carry what every rule of the envs needs — obstacle (< 0), walkable (>= 0), counted (> 0).
+    The one place the reference reads a cell's VALUE is SuperGridRL's coverage reward (``reward += grid[j][k]``,
+    super_grid_rl.py:189, sim_env.py:159): maps with free cells worth something other than 1 keep their values
+    in a float64 table next to the planes (PNG maps give exactly -1 / +1 and need none)."""
     arr = np.stack([np.asarray(g, dtype=np.float64) for g in grids])
+    if not np.all(np.isfinite(arr)):
+        raise ValueError("maps must hold finite cell values")
     cells = np.sign(arr).astype(np.int8)
-    if not np.array_equal(np.where(arr > 0, 1.0, np.where(arr < 0, -1.0, 0.0)), arr):
-        raise ValueError("maps must hold only -1 / 0 / +1 cells (PNG maps do); per-cell reward "
-                         "values other than 1 are outside this build's scope")
-    return cells
+    unit = np.array_equal(np.where(arr > 0, 1.0, np.where(arr < 0, -1.0, 0.0)), arr)
+    return cells, (None if unit else np.where(arr > 0, arr, 0.0))
 
 
 # ---- host-side (numpy) view of the strip-major layout: used by tests and get_state --------------
@@ -116,10 +121,22 @@ class MapTable:
     def __init__(self, grids, add_border, device):
         import torch
         lib = _lib.load()
-        cells = grids_to_cells(grids)
+        cells, values = grids_to_cells(grids)
+        if add_border:
+            # DecGridRL never reads a cell's value for its reward (a count, dec_grid_rl.py:243-256), but its square
+            # sensor stores np.clip(cell, 0, 1) / np.clip(-cell, 0, 1) in the robots' float maps
+            # (squaresensor.py:34-35): magnitudes >= 1 clip to exactly 1 and are fine, magnitudes inside (0, 1)
+            # would make those maps fractional, which bit planes cannot hold
+            mag = np.abs(np.stack([np.asarray(g, dtype=np.float64) for g in grids]))
+            if np.any((mag > 0) & (mag < 1)):
+                raise ValueError("DecGridRL maps must not hold cell values of magnitude inside (0, 1): the reference's "
+                                 "square sensor would store them as fractional known-free / known-obstacle values")
+            values = None
         M, W, L = cells.shape
         self._alloc(M, W, L, add_border, device)
         with torch.cuda.device(self.device):
+            # float64 [M, W, L] reward of covering each free cell (map coordinates, no border), or None = all 1.0
+            self.values = None if values is None else torch.from_numpy(values).to(self.device).contiguous()
             cells_dev = torch.from_numpy(cells).to(self.device)
             b = 1 if add_border else 0
             st = torch.cuda.current_stream(self.device).cuda_stream
@@ -134,6 +151,7 @@ class MapTable:
         self.n_maps, self.W, self.L = M, W + 2 * b, L + 2 * b
         self.strips, self.Wp, self.plane_words = _lib.plane_geometry(self.W, self.L)
         self.device = torch.device(device)
+        self.values = None
         with torch.cuda.device(self.device):
             self.wall = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
             self.pos = torch.empty((M, self.plane_words), dtype=torch.int32, device=self.device)
@@ -166,4 +184,6 @@ class MapTable:
         g = np.where(wall, -1.0, np.where(pos, 1.0, 0.0))
         if b:
             g = g[:, 1:-1, 1:-1]
+        if self.values is not None:
+            g = np.where(g > 0, self.values.cpu().numpy(), g)
         return [np.array(m) for m in g]

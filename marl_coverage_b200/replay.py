@@ -109,7 +109,9 @@ class ReplayBuffer(object):
         """Rows ``indices`` (int64, host or device) of all five arrays, one launch."""
         import torch
         idx = torch.as_tensor(np.asarray(indices) if not torch.is_tensor(indices) else indices)
-        idx = idx.to(device=self.device, dtype=torch.int64).reshape(-1).contiguous()
+        if not idx.is_cuda and idx.numel() and (int(idx.min()) < 0 or int(idx.max()) >= self._maxsize):
+            raise IndexError("replay indices outside [0, %d)" % self._maxsize)   # host values: checked here for free
+        idx = idx.to(device=self.device, dtype=torch.int64).reshape(-1).contiguous()   # device values: clamped by the kernel
         B = int(idx.numel())
         f32 = dict(dtype=torch.float32, device=self.device)
         st = torch.empty((B,) + tuple(self._state.shape[1:]), **f32)
@@ -119,7 +121,7 @@ class ReplayBuffer(object):
         dn = torch.empty((B,), **f32)
         with torch.cuda.device(self.device):
             _lib.check(self._lib.mcov_replay_gather(
-                idx.data_ptr(), B, self._row, self._adim, self._state.data_ptr(), self._nextstate.data_ptr(),
+                idx.data_ptr(), self._maxsize, B, self._row, self._adim, self._state.data_ptr(), self._nextstate.data_ptr(),
                 self._action.data_ptr(), self._reward.data_ptr(), self._done.data_ptr(), st.data_ptr(),
                 nx.data_ptr(), ac.data_ptr(), rw.data_ptr(), dn.data_ptr(), self._stream()))
         self._keep_idx = idx

@@ -55,6 +55,9 @@ class _VecEnv:
             _lib.check(self._lib.mcov_set_maps(self._handle, self.maps.wall.data_ptr(),
                                                self.maps.pos.data_ptr(), self.maps.free_counts.data_ptr(),
                                                self.maps.n_maps, self.maps.W, self.maps.L))
+            if self.ENV_TYPE == _lib.ENV_SUPER and self.maps.values is not None:
+                # free cells worth something other than 1 (super_grid_rl.py:189); DecGridRL's reward is a count
+                _lib.check(self._lib.mcov_set_cell_values(self._handle, self.maps.values.data_ptr()))
             lay = _lib.McovLayout()
             _lib.check(self._lib.mcov_state_layout(self._handle, C.byref(lay)))
             self.layout = lay
@@ -144,8 +147,9 @@ class _VecEnv:
         Returns the float32 CUDA observation tensor (written in place into ``out`` or ``self.obs``)."""
         import torch
         obs = self.obs if out is None else self._check_obs_out(out)
-        mi = self._as_dev(map_idx, torch.int32, (self.num_envs,))
-        sx = self._as_dev(start_xy, torch.int16, (self.num_envs, self.num_robots, 2))
+        mi = self._as_dev(map_idx, torch.int32, (self.num_envs,), lo=0, hi=self.maps.n_maps)
+        sx = self._as_dev(start_xy, torch.int16, (self.num_envs, self.num_robots, 2), lo=0,
+                          hi=(self.W, self.L))
         mk = self._as_dev(mask, torch.uint8, (self.num_envs,))
         if seed is None:
             seed = (self.seed + 0x9E3779B97F4A7C15 * self._reset_calls) & 0xFFFFFFFFFFFFFFFF
@@ -266,11 +270,19 @@ class _VecEnv:
         return int(self._lib.mcov_launch_count(self._handle))
 
     # -- state access (get_state / set_state through the arena layout) ----------------------------
-    def _as_dev(self, x, dtype, shape):
+    def _as_dev(self, x, dtype, shape, lo=None, hi=None):
+        """Host values are range-checked here, where it is free ([lo, hi), hi per last-axis column when a tuple);
+        values that already live on the device cannot be looked at without a sync and are clamped by the kernels."""
         import torch
         if x is None:
             return None
         t = x if torch.is_tensor(x) else torch.as_tensor(np.asarray(x))
+        if lo is not None and not t.is_cuda and t.numel():
+            his = hi if isinstance(hi, tuple) else (hi,)
+            for k, h in enumerate(his):
+                col = t[..., k] if isinstance(hi, tuple) else t
+                if int(col.min()) < lo or int(col.max()) >= h:
+                    raise ValueError("value outside [%d, %d) in %s input" % (lo, h, tuple(shape)))
         t = t.to(device=self.device, dtype=dtype).contiguous()
         if tuple(t.shape) != tuple(shape):
             raise ValueError("expected shape %s, got %s" % (tuple(shape), tuple(t.shape)))

@@ -55,6 +55,18 @@ def small_maps():
     return train + test
 
 
+def valued(maps, seed, worths=(0.0, 0.25, 1.0, 2.5, 3.0, 0.1)):
+    """The same maps with free cells worth 0 / 0.25 / 1 / 2.5 / 3 / 0.1 instead of 1: the reference pays
+    ``reward += self._grid[j][k]`` (super_grid_rl.py:189), counts ``grid > 0`` and walks on ``grid >= 0``."""
+    rng = np.random.RandomState(seed)
+    out = []
+    for m in maps:
+        m = np.asarray(m, dtype=np.float64)
+        worth = rng.choice(list(worths), size=m.shape)
+        out.append(np.where(m > 0, worth, m * rng.choice([1.0, 2.0], size=m.shape)))
+    return out
+
+
 class Mismatch(Exception):
     pass
 
@@ -200,6 +212,16 @@ def main():
         ("super_dist_reward", "super", m15, super_cfg(dist_reward=1, numrobot=3), 200, 24, {}),
         ("super_15x15_r1", "super", m15, super_cfg(senseradius=1, numrobot=2), 300, 25, {}),
         ("super_n9", "super", m100, super_cfg(numrobot=9, senseradius=3), 150, 26, {}),
+        ("super_cell_values", "super", valued(m15, 1), super_cfg(numrobot=3, senseradius=1, done_thresh=0.6), 250, 27,
+         {"episodes": 3}),
+        ("super_cell_values_100_scanning", "super", valued(m100[:2], 2), super_cfg(use_scanning=1, free_penalty=0.37),
+         150, 28, {"episodes": 1}),
+        # DecGridRL: the square sensor stores clip(cell, 0, 1), so magnitudes >= 1 behave like +-1 (and 0 = walkable,
+        # never known-free); the reward stays a count
+        ("dec_cell_values_clip", "dec", valued(m15, 3, (0.0, 1.0, 2.5, 3.0)),
+         dec_cfg(numrobot=2, egoradius=3, done_thresh=0.5), 150, 29, {}),
+        ("dec_cell_values_clip_lidar", "dec", valued(m15, 4, (0.0, 1.0, 2.5, 3.0)),
+         dec_cfg(numrobot=2, egoradius=3, sensor_type="lidar", sensor_config={"num_lasers": 9, "range": 4}), 100, 30, {}),
     ]
     report = {"reference_root": rh.REFERENCE_ROOT, "numpy": np.__version__,
               "when": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime()), "cases": {}}

@@ -31,8 +31,12 @@ def test_builtin_and_committed_grid_sets():
     assert set(np.unique(g100[0])) <= {-1.0, 1.0}
     tr, te = maps.gridload({"grid_dir": "./Grids/bg2_100x100", "numgrids": 20})
     assert len(tr) == 10 and len(te) == 10             # gridmaker.py:96-102 half split
+    cells, values = maps.grids_to_cells([np.full((4, 4), 0.5), np.array([[-2.0, 0.0, 3.0, 1.0]] * 4)])
+    assert cells[0].tolist() == [[1] * 4] * 4 and cells[1][0].tolist() == [-1, 0, 1, 1]
+    assert values[0, 0, 0] == 0.5 and values[1][0].tolist() == [0.0, 0.0, 3.0, 1.0]      # free cells keep their worth
+    assert maps.grids_to_cells(g100[:2])[1] is None                                       # +-1 PNG maps need no table
     with pytest.raises(ValueError):
-        maps.grids_to_cells([np.full((4, 4), 0.5)])
+        maps.grids_to_cells([np.full((4, 4), np.nan)])
 
 
 def test_gridgen_matches_reference_contract():

@@ -200,7 +200,7 @@ def test_bad_configs_are_refused():
     with pytest.raises(_lib.McovError):
         VecSuperGridRL(g, dict(_super_cfg(np.random.default_rng(0), 2), senseradius=16), num_envs=2)
     with pytest.raises((ValueError, _lib.McovError)):
-        VecDecGridRL([np.full((10, 10), 2.0)], base, num_envs=2)      # cell values other than -1 / 0 / +1
+        VecDecGridRL([np.full((10, 10), np.inf)], base, num_envs=2)   # cell values must be finite
     # 32-bit plane offsets: refused with a message before any arena is allocated
     with pytest.raises(_lib.McovError, match="shard the batch"):
         VecDecGridRL([np.ones((1073, 1073))], dict(base, numrobot=16), num_envs=8000)
