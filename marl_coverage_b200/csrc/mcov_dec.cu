@@ -401,11 +401,14 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 const int i = div_s(idx), r = idx - i * S;
                 const uint32_t pi = sm.posF[i];
                 const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
-                sm.wallW[idx] = (x >= 0 && x < W) ? read_window(wall_g + map_off, Wp, strips, x, y0, S) : 0xffffffffu;
-                // table walk: every beam starts on the robot's own (walkable) cell, lidar.py:30 — set it here
-                // once instead of by n_lasers colliding shared-memory atomics
-                sm.winF[idx] = (p.lidar_cells && r == R) ? (1u << R) : 0u;
-                sm.winO[idx] = 0;
+                const uint32_t wrow = (x >= 0 && x < W) ? read_window(wall_g + map_off, Wp, strips, x, y0, S) : 0xffffffffu;
+                sm.wallW[idx] = wrow;
+                // table walk: every beam starts on the robot's own cell, lidar.py:30 — set it here once instead of
+                // by n_lasers colliding shared-memory atomics.  (A robot never stands on an obstacle inside the env;
+                // a sensor probe can put one there: then every beam ends at once on that cell, lidar.py:58-63.)
+                const bool own_wall = (wrow >> R) & 1u;
+                sm.winF[idx] = (p.lidar_cells && r == R && !own_wall) ? (1u << R) : 0u;
+                sm.winO[idx] = (p.lidar_cells && r == R && own_wall) ? (1u << R) : 0u;
             }
             g.sync();
             if (p.lidar_cells) {
@@ -422,6 +425,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     const uint32_t* ww = sm.wallW + i * S;
                     uint32_t* wf = sm.winF + i * S;
                     uint32_t* wo = sm.winO + i * S;
+                    if ((ww[R] >> R) & 1u) continue;               // own cell is an obstacle: the beam ended there
 #pragma unroll
                     for (int k = 1; k < 16; ++k) {
                         const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
