@@ -9,8 +9,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmcov_b200.so")
-SOURCES = ["mcov_api.cu", "mcov_dec.cu", "mcov_super.cu", "mcov_extras.cu", "mcov_replay.cu", "mcov_aux.cu"]
-HEADERS = ["mcov_common.cuh", "mcov_dt.cuh", "mcov_internal.h", os.path.join("..", "..", "include", "mcov.h")]
+SOURCES = ["mcov_api.cu", "mcov_dec.cu", "mcov_dec_cta.cu", "mcov_super.cu", "mcov_extras.cu", "mcov_replay.cu", "mcov_aux.cu"]
+HEADERS = ["mcov_common.cuh", "mcov_dec_shared.cuh", "mcov_dt.cuh", "mcov_internal.h", os.path.join("..", "..", "include", "mcov.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "--expt-relaxed-constexpr"]

@@ -292,6 +292,15 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
     if (ce != cudaSuccess) { delete e; return cuda_fail(ce, "cudaDeviceGetAttribute"); }
     e->obs_C = obs_channels(c);
     e->debug = getenv("MCOV_DEBUG") ? atoi(getenv("MCOV_DEBUG")) : 0;
+    auto pin = [](const char* name) { const char* v = getenv(name); return v && *v ? atoi(v) : -1; };
+    e->pin_group = pin("MCOV_DEC_GROUP");
+    e->pin_store = pin("MCOV_DEC_STORE");
+    e->pin_grid = pin("MCOV_DEC_GRID");
+    e->pin_nbuf = pin("MCOV_DEC_NBUF");
+    e->pin_shape = pin("MCOV_DEC_SHAPE");
+    e->pin_sw = pin("MCOV_DEC_SW");
+    e->pin_rot = pin("MCOV_DEC_ROT");
+    e->pin_tma = pin("MCOV_DEC_TMA");
     *out = e;
     return MCOV_OK;
 }

@@ -29,28 +29,16 @@
 #include <stdlib.h>
 
 #include "mcov_internal.h"
+#include "mcov_dec_shared.cuh"
 
 namespace mcov {
 
 namespace {
 
-constexpr unsigned FULL = 0xffffffffu;
 constexpr int MAX_WARPS = 8;
 #ifndef MCOV_DEC_MINB
 #define MCOV_DEC_MINB 4                      // resident 256-thread CTAs per SM the register budget is set for
 #endif
-
-// floor(k / d) for k < 2^26, d <= 64, magic = ceil(2^32 / d)
-// (d == 1 gives magic = 2^32 = 0 in 32 bits: the quotient is k itself)
-__device__ __forceinline__ int fast_div(int k, uint32_t magic) {
-    return magic ? (int)__umulhi((uint32_t)k, magic) : k;
-}
-
-// Draws map + start poses on the device (see draw_starts in mcov_common.cuh).
-__device__ void draw_reset(const DecParams& p, int e, uint32_t episode, uint32_t* posS, int* map_out) {
-    draw_starts(p.wall, p.g, p.N, p.n_maps, p.map_idx_in, p.start_xy_in, p.seed,
-                (uint32_t)(p.env_id_base + e), e, episode, posS, map_out);
-}
 
 // ---- lane groups: G consecutive lanes (8, 16 or 32) own one env; a warp steps 32/G envs at once.
 // Every warp-level primitive below names only the group's lanes, so groups of one warp may diverge
@@ -114,7 +102,7 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
     GroupSmem s;
     s.stats = reinterpret_cast<double*>(base);
     s.bits = reinterpret_cast<uint32_t*>(base + MCOV_STATS_LEN * 8);
-    s.posF = s.bits + p.bits_words;
+    s.posF = s.bits + (p.st_slot_words ? 2 * p.st_slot_words : p.bits_words);   // Spec::ST: two bit-stream slots
     s.nearM = s.posF + p.N;
     s.covS = reinterpret_cast<int*>(s.nearM + p.N);
     s.winF = reinterpret_cast<uint32_t*>(s.covS + p.N);
@@ -123,57 +111,45 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
     return s;
 }
 
-__device__ __forceinline__ void prefetch_l1(const void* ptr) {
-    asm volatile("prefetch.global.L1 [%0];" :: "l"(ptr));
-}
-__device__ __forceinline__ void prefetch_l2(const void* ptr) {
-    asm volatile("prefetch.global.L2 [%0];" :: "l"(ptr));
-}
-#ifndef MCOV_ST_MODE
-#define MCOV_ST_MODE 0                       // observation store policy: 0 .cs  1 default  2 .cg  3 .wt
-#endif
-__device__ __forceinline__ void obs_store(float4* ptr, const float4 v) {
-#if MCOV_ST_MODE == 0
-    __stcs(ptr, v);
-#elif MCOV_ST_MODE == 1
-    *ptr = v;
-#elif MCOV_ST_MODE == 2
-    __stcg(ptr, v);
-#else
-    __stwt(ptr, v);
-#endif
-}
 #ifndef MCOV_PF_NEXT
 #define MCOV_PF_NEXT 0                       // measured on B200 (C5): 0.213 -> 0.233 ms with it on — the step is DRAM-throughput bound, extra line fetches cost more than the latency they hide
 #endif
-
-// ORs `v` into the bit stream at bit offset `off` (shared-memory atomics:
-// neighbouring rows share words).
-__device__ __forceinline__ void stream_or(uint32_t* bits, int off, uint32_t v) {
-    const int w = off >> 5, sh = off & 31;
-    const uint32_t lo = v << sh, hi = __funnelshift_l(v, 0u, sh);   // bits of v pushed past bit 31
-    if (lo) atomicOr(bits + w, lo);
-    if (hi) atomicOr(bits + w + 1, hi);
-}
-
-// Sensor-frame helpers.  A robot at (xj, yj) with range R touches, in map row x (|x - xj| <= R),
-// the cells y in [yj-R, yj+R]; `ymask_in_strip` is that interval cut to absolute strip s.
-__device__ __forceinline__ uint32_t ymask_in_strip(int yj, int R, int S, int s) {
-    const int y0 = yj - R, s0 = y0 >> 5;
-    const uint64_t m = (uint64_t)low_mask(S) << (y0 & 31);
-    return s == s0 ? (uint32_t)m : (s == s0 + 1 ? (uint32_t)(m >> 32) : 0u);
-}
 
 // One pass over env e in `mode`.  Returns true when a finished env must be re-seeded in place by a
 // second (MODE_RESET) pass of the same lane group (fused auto-reset).
 // Compile-time shape of an env (0 = read the value from DecParams at run time).  The named
 // BASELINE configs get their own instantiation so that loop bounds, divisions and masks fold.
-template <int G_, bool LIDAR_, int CN_, int CR_, int CE_>
+template <int G_, bool LIDAR_, int CN_, int CR_, int CE_, bool ST_ = false>
 struct Spec {
     static constexpr int G = G_, CN = CN_, CR = CR_, CE = CE_;
     static constexpr bool LIDAR = LIDAR_;
     static constexpr bool FIXED = CN_ > 0;             // then C == 3, N, R, ego are constants
+    static constexpr bool ST = ST_;                    // observation blocks leave through the CTA's store warp (TMA bulk stores)
 };
+
+// ---- store-warp hand-over (Spec::ST) -------------------------------------------------------------
+// The lane groups of the pass warps do not write their observation block themselves: a group fills one of
+// its two bit-stream slots and signals the slot's `full` mbarrier; the CTA's last warp (the store warp)
+// expands a full slot into a float32 staging buffer in shared memory, frees the slot (`empty` mbarrier) and
+// hands the whole block to the TMA engine (cp.async.bulk shared -> global, one 5.8 kB burst per env at C2).
+// Pass warps therefore never wait for store issue, and DRAM sees whole-block bursts from 4 store warps per
+// SM instead of 128 lane groups each trickling 16-byte stores (tools/ubench/store_patterns.cu: 4.65 -> 6.0 TB/s).
+struct StoreLink {
+    uint32_t pub, con;        // shared-memory addresses of this group's counters: blocks published / consumed
+    int it;                   // blocks published so far by this group (slot = it & 1)
+};
+__device__ __forceinline__ uint32_t ld_acquire_smem(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_smem(uint32_t addr, uint32_t v) {
+    asm volatile("st.release.cta.shared.u32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
+}
+// slot it & 1 was last used by block it - 2: wait until the store warp has consumed it
+__device__ __forceinline__ void wait_slot_free(const StoreLink& link) {
+    while ((int)ld_acquire_smem(link.con) < link.it - 1) __nanosleep(32);
+}
 
 // While this env's observation block streams out, start the DRAM reads the group's NEXT env will need:
 // the lines under every robot's band in its own {free, obst} planes, the union plane and the two truth
@@ -213,12 +189,12 @@ __device__ __forceinline__ void prefetch_next_env(const DecParams& p, const Pref
     }
 }
 
-enum { PASS_DONE = 0, PASS_AGAIN = 2 };   // env_pass results
 
 template <class SP>
 __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut,
                                          const int e, const int mode, const Prefetch& cur,
-                                         const Grp<SP::G>& g, const Prefetch& nxt, const int e_next) {
+                                         const Grp<SP::G>& g, const Prefetch& nxt, const int e_next,
+                                         const StoreLink& link) {
     constexpr int G = SP::G;
     constexpr bool LIDAR = SP::LIDAR;
     const int N = SP::FIXED ? SP::CN : p.N, R = SP::FIXED ? SP::CR : p.R, ego = SP::FIXED ? SP::CE : p.ego;
@@ -336,6 +312,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
         sm.nearM[lg] = 0;
         if (mode != MODE_OBSERVE && (fresh || newv != myv)) hpos[lg] = newv;
     }
+    if (SP::ST) wait_slot_free(link);          // the store warp has finished reading this slot
     for (int k = lg; k < p.bits_words; k += G) sm.bits[k] = 0;
 
     // ---- communication graph (dec_grid_rl.py:374-391): Chebyshev ball, diagonal included ------
@@ -665,6 +642,15 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
 #if MCOV_PF_NEXT
     if (e_next >= 0) prefetch_next_env<SP>(p, nxt, e_next, g);
 #endif
+    if (SP::ST) {
+        // hand the bit stream to the store warp: every lane's ORs into the slot are ordered before the
+        // leader's store by the group barrier above; the store is a release at CTA scope
+        if (lg == 0) {
+            sm.bits[p.bits_words] = (p.debug & 1) ? 0xffffffffu : (uint32_t)e;
+            st_release_smem(link.pub, (uint32_t)link.it + 1u);
+        }
+        return PASS_DONE;
+    }
     if (p.debug & 1) return PASS_DONE;                             // MCOV_DEBUG=1: profiling aid, no obs store
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
@@ -692,20 +678,41 @@ dec_env_kernel(const DecParams p) {
     __shared__ float4 lut[16];
     __shared__ int last_flag;
     const Grp<G> g(threadIdx.x & 31);
-    const int gpc = blockDim.x / G;                       // lane groups (= envs in flight) per CTA
-    const int gi = threadIdx.x / G;
-    const GroupSmem sm = carve(smem_raw + (size_t)gi * p.grp_smem, p);
+    // Spec::ST: st_warps of the CTA's warps are store warps, the others are pass warps.  The store warps of the
+    // CTAs resident on one SM must not share a warp scheduler (warp w issues on sub-partition w % 4; a store
+    // warp carries a quarter of the SM's expansion work): CTA b takes warp (b / num_sms) % 4, i.e. the four CTAs
+    // a persistent grid puts on an SM take four different sub-partitions.
+    const int pass_threads = SP::ST ? (int)blockDim.x - 32 * p.st_warps : (int)blockDim.x;
+    const int gpc = pass_threads / G;                     // lane groups (= envs in flight) per CTA
+    const int wid = threadIdx.x >> 5;
+    const int sw_first = SP::ST ? (p.st_rot_div > 0 ? (int)((blockIdx.x / (unsigned)p.st_rot_div) & 3u) : (pass_threads >> 5)) : 0;
+    const bool store_warp = SP::ST && wid >= sw_first && wid < sw_first + p.st_warps;
+    const int pass_tid = (SP::ST && wid >= sw_first + p.st_warps) ? (int)threadIdx.x - 32 * p.st_warps : (int)threadIdx.x;
+    const int gi = store_warp ? 0 : pass_tid / G;
+    GroupSmem sm = carve(smem_raw + (size_t)gi * p.grp_smem, p);
+    uint32_t* const bits0 = sm.bits;
+    const uint32_t ctr0 = smem_u32(smem_raw + p.st_bar_off);   // uint32 pub[gpc] (blocks published), con[gpc] (consumed)
 
     if (threadIdx.x < 16) {
         const uint32_t t = threadIdx.x;
         lut[t] = make_float4((t & 1u) ? 1.0f : 0.0f, (t & 2u) ? 1.0f : 0.0f, (t & 4u) ? 1.0f : 0.0f,
                              (t & 8u) ? 1.0f : 0.0f);
     }
-    for (int k = g.lg; k < MCOV_STATS_LEN; k += G) sm.stats[k] = 0.0;
+    if (!store_warp)
+        for (int k = g.lg; k < MCOV_STATS_LEN; k += G) sm.stats[k] = 0.0;
+    if (SP::ST)
+        for (int k = threadIdx.x; k < gpc * 2; k += blockDim.x)
+            reinterpret_cast<uint32_t*>(smem_raw + p.st_bar_off)[k] = 0u;
     __syncthreads();
 
-    const int gg = blockIdx.x * gpc + gi, gtot = gridDim.x * gpc;
+    const int gtot = gridDim.x * gpc;
     const int mode = p.mode;
+    if (!store_warp) {
+    const int gg = blockIdx.x * gpc + gi;
+    StoreLink link;
+    link.pub = ctr0 + 4u * gi;
+    link.con = ctr0 + 4u * (gpc + gi);
+    link.it = 0;
     Prefetch nxt;
     nxt.pos = 0; nxt.act8 = 0; nxt.act64 = 0; nxt.map_idx = 0; nxt.shown = 0;
     if (mode != MODE_RESET && gg < p.E) nxt = load_prefetch(p, gg, g.lg);
@@ -713,13 +720,24 @@ dec_env_kernel(const DecParams p) {
         const Prefetch cur = nxt;
         if (mode != MODE_RESET && e + gtot < p.E) nxt = load_prefetch(p, e + gtot, g.lg);
         int m = mode;
+        if (SP::ST) sm.bits = bits0 + (link.it & 1) * p.st_slot_words;
         if (m == MODE_RESET) {
             int act = 1;
             if (p.mask) act = p.mask[e];
             else if (p.mask_from_flags) act = p.needs_reset[e];
-            if (!act) continue;                                    // group-uniform
+            if (!act) {                                            // group-uniform
+                if (SP::ST) {                                      // the store warp counts slots: publish an empty one
+                    wait_slot_free(link);
+                    if (g.lg == 0) {
+                        sm.bits[p.bits_words] = 0xffffffffu;
+                        st_release_smem(link.pub, (uint32_t)link.it + 1u);
+                    }
+                    ++link.it;
+                }
+                continue;
+            }
         }
-        if (p.debug & 2) {                                         // MCOV_DEBUG=2: profiling aid, obs store only
+        if (!SP::ST && (p.debug & 2)) {                            // MCOV_DEBUG=2: profiling aid, obs store only
             float4* d = reinterpret_cast<float4*>(p.obs + (size_t)e * p.obs_env_floats) + g.lg;
             const int iters = ((p.obs_env_floats >> 2) - g.lg + G - 1) / G;
 #pragma unroll 4
@@ -730,40 +748,83 @@ dec_env_kernel(const DecParams p) {
             continue;
         }
         const int e_next = (mode == MODE_STEP && e + gtot < p.E) ? e + gtot : -1;
-        while (env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
+        while (env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next, link) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
+        ++link.it;
+    }
+    } else {
+        // ---- store warp: full slot -> float32 staging buffer -> one TMA bulk store per env block ----
+        // Store warp sw serves lane groups sw, sw + nsw, ...; its lane l tracks group l * nsw + sw: how many of
+        // that group's blocks have been taken, how many it will publish.  One shared-memory load polls them all.
+        const int lane = threadIdx.x & 31, nsw = p.st_warps, sw = wid - sw_first;
+        const int mygrp = lane * nsw + sw;
+        int taken = 0, mine = 0;
+        if (mygrp < gpc) {
+            const int gg = blockIdx.x * gpc + mygrp;
+            if (gg < p.E) mine = (p.E - gg + gtot - 1) / gtot;
+        }
+        int left = (int)__reduce_add_sync(FULL, mine);
+        const int nf4 = p.obs_env_floats >> 2;
+        const uint32_t blk_bytes = (uint32_t)p.obs_env_floats * 4u;
+        const int nbuf = p.st_nbuf;
+        unsigned char* const stage0 = smem_raw + p.st_stage_off + (size_t)sw * nbuf * p.st_stage_pitch;
+        const uint32_t my_pub = ctr0 + 4u * (mygrp < gpc ? mygrp : 0);
+        int buf = 0;
+        while (left > 0) {
+            const bool ready = taken < mine && (int)ld_acquire_smem(my_pub) > taken;
+            uint32_t rm = __ballot_sync(FULL, ready);
+            if (!rm) { __nanosleep(32); continue; }
+            for (; rm; rm &= rm - 1) {
+                const int src = __ffs(rm) - 1, sgrp = src * nsw + sw;
+                const int tk = __shfl_sync(FULL, taken, src);
+                const uint32_t* bits = reinterpret_cast<const uint32_t*>(smem_raw + (size_t)sgrp * p.grp_smem + MCOV_STATS_LEN * 8) +
+                                       (tk & 1) * p.st_slot_words;
+                const uint32_t eid = bits[p.bits_words];
+                if (eid != 0xffffffffu && !(p.debug & 4)) {          // MCOV_DEBUG=4: profiling aid, hand-over only
+                    if (lane == 0) {                               // the staging buffer about to be refilled has been read out
+                        if (nbuf == 4) asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+                        else if (nbuf == 3) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+                        else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    }
+                    __syncwarp();
+                    float4* stage = reinterpret_cast<float4*>(stage0 + (size_t)buf * p.st_stage_pitch);
+                    // bits, table and staging buffer are all shared memory: the loads of a batch are issued before its
+                    // stores by hand, or every store would order the next load behind it (possible aliasing)
+                    const int sh4 = (lane & 7) * 4;
+                    for (int q0 = lane; q0 < nf4; q0 += 32 * 6) {
+                        uint32_t nib[6];
+                        float4 v[6];
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) {
+                            const int q = q0 + 32 * j;
+                            nib[j] = q < nf4 ? (bits[q >> 3] >> sh4) & 15u : 0u;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) v[j] = lut[nib[j]];
+#pragma unroll
+                        for (int j = 0; j < 6; ++j)
+                            if (q0 + 32 * j < nf4) stage[q0 + 32 * j] = v[j];
+                    }
+                    fence_proxy_async_smem();                      // generic-proxy writes -> visible to the TMA engine
+                    __syncwarp();
+                    if (lane == 0) {
+                        st_release_smem(ctr0 + 4u * (gpc + sgrp), (uint32_t)tk + 1u);   // slot is free again
+                        if (!(p.debug & 8))                        // MCOV_DEBUG=8: profiling aid, expansion without the bulk store
+                            bulk_store_s2g(p.obs + (size_t)eid * p.obs_env_floats, stage, blk_bytes);
+                    }
+                    buf = buf + 1 == nbuf ? 0 : buf + 1;
+                } else {
+                    __syncwarp();
+                    if (lane == 0) st_release_smem(ctr0 + 4u * (gpc + sgrp), (uint32_t)tk + 1u);
+                }
+                if (lane == src) ++taken;
+                --left;
+            }
+        }
+        if (lane == 0) bulk_wait_all();                            // smem is read out and the blocks are written before the CTA ends
     }
 
     // ---- episode statistics: group sums -> CTA row -> last CTA folds all rows (single launch) --
-    if (p.stats_out) {
-        __syncthreads();
-        if (threadIdx.x < MCOV_STATS_LEN) {
-            double s = 0.0;
-            for (int w = 0; w < gpc; ++w)
-                s += reinterpret_cast<const double*>(smem_raw + (size_t)w * p.grp_smem)[threadIdx.x];
-            p.stats_partial[(size_t)blockIdx.x * MCOV_STATS_LEN + threadIdx.x] = s;
-        }
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) last_flag = (atomicAdd(p.counter, 1u) == gridDim.x - 1) ? 1 : 0;
-        __syncthreads();
-        if (last_flag) {
-            __threadfence();
-            double* red = reinterpret_cast<double*>(smem_raw);      // all groups are done with smem
-            const int k = threadIdx.x & (MCOV_STATS_LEN - 1), r0 = threadIdx.x >> 3, rstep = blockDim.x >> 3;
-            double s = 0.0;
-            for (int r = r0; r < (int)gridDim.x; r += rstep)
-                s += __ldcg(p.stats_partial + (size_t)r * MCOV_STATS_LEN + k);
-            __syncthreads();
-            red[threadIdx.x] = s;
-            __syncthreads();
-            if (threadIdx.x < MCOV_STATS_LEN) {
-                double t = 0.0;
-                for (int r = 0; r < rstep; ++r) t += red[r * MCOV_STATS_LEN + threadIdx.x];
-                p.stats_out[threadIdx.x] = t;
-            }
-            if (threadIdx.x == 0) *p.counter = 0u;
-        }
-    }
+    fold_episode_stats(p, smem_raw, gpc, (size_t)p.grp_smem, reinterpret_cast<double*>(smem_raw), &last_flag);
 }
 
 // ---- shareMaps (dec_grid_rl.py:423-447): free_i/obst_i <- OR over linked robots, then recount ---
@@ -843,9 +904,13 @@ struct DecLaunchShape {
     int G, threads, grid;
     size_t grp_smem, smem;
     int bits_words;
+    // store-warp variant (Spec::ST): 0 = off
+    int st, slot_words, nbuf, bar_off, stage_off, stage_pitch, nsw;
 };
 
-inline int pick_group(const mcov_config& c, int num_sms) {
+inline int pick_group(const mcov_env* env) {
+    const mcov_config& c = env->cfg;
+    const int num_sms = env->num_sms;
     // lanes per env: at least the robots (poses live in lanes).  With many envs 8 lanes per env keep
     // the one-lane phases (moves, bookkeeping) shared by 4 envs per warp; with few envs (E * G below
     // the resident thread capacity) wider groups cut the per-env latency instead: a step of 4096
@@ -862,52 +927,93 @@ inline int pick_group(const mcov_config& c, int num_sms) {
     const long long capacity = (long long)num_sms * 4 * MAX_WARPS * 32;      // resident threads
     while (g < 32 && (long long)c.num_envs * (2 * g) <= capacity) g *= 2;
     // MCOV_DEC_GROUP=8|16|32 pins the width (tests run every width on the same traces; tuning)
-    if (const char* f = getenv("MCOV_DEC_GROUP")) {
-        const int v = atoi(f);
+    {
+        const int v = env->pin_group;
         if ((v == 4 || v == 8 || v == 16 || v == 32) && v >= c.num_robots) g = v;
     }
     return g;
 }
 
-inline DecLaunchShape dec_shape(const mcov_env* env) {
+// Store-warp variant: parity-green, measured on B200 at C5 (profiles/r02_ab.jsonl) and SLOWER than the direct
+// stores — 0.227-0.277 ms against 0.213 ms: the lane groups of a CTA publish in a convoy, one store warp expands
+// about one block per microsecond, and the waiting groups spin (ncu: a third of all instructions in
+// wait_slot_free).  It stays selectable (MCOV_DEC_STORE=1, read at mcov_create) as the TMA bulk-store arm of
+// that A/B and is covered by the parity tests; the default is the direct path.
+inline bool want_store_warp(const mcov_env* env, int G, bool vec_ok) {
+    const mcov_config& c = env->cfg;
+    const int ow = 2 * c.egoradius + 1;
+    const long long blk = (long long)c.num_robots * env->obs_C * ow * ow * 4;
+    if (!vec_ok || blk % 16 != 0 || blk > 12 * 1024 || G == 4) return false;
+    return env->pin_store > 0;
+}
+
+inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
     const mcov_config& c = env->cfg;
     const int N = c.num_robots, S = 2 * c.sensor_range + 1, ow = 2 * c.egoradius + 1;
     DecLaunchShape s;
-    s.G = pick_group(c, env->num_sms);
+    s.G = pick_group(env);
+    s.st = want_store_warp(env, s.G, vec_ok) ? 1 : 0;
     s.bits_words = (N * env->obs_C * ow * ow + 31) / 32 + 1;
-    int words = s.bits_words + 3 * N + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 * N * S : 0);
+    s.slot_words = s.st ? round_up(s.bits_words + 1, 2) : 0;       // + the env id word
+    s.nbuf = 0; s.bar_off = 0; s.stage_off = 0; s.stage_pitch = 0; s.nsw = 1;
+    int words = (s.st ? 2 * s.slot_words : s.bits_words) + 3 * N + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 * N * S : 0);
     words = round_up(words, 2);
     // stagger the groups of one warp over the 32 banks: stride = multiple of 32 words + G
     int stride_words = MCOV_STATS_LEN * 2 + words;
     if (s.G < 32) stride_words = round_up(stride_words, 32) + s.G;
     s.grp_smem = (size_t)stride_words * 4;
-    // CTA size: the one that keeps the most lane groups resident per SM (shared memory is the limit
-    // for lidar windows: 2 x 83 kB CTAs hold 64 groups where 5 x 41 kB CTAs hold 80)
     const int per_warp = 32 / s.G;
-    int groups = per_warp, per_sm = 1, best = 0;
-    for (int warps = MAX_WARPS; warps >= 1; warps >>= 1) {
-        const int gr = warps * per_warp;
-        size_t sm_bytes = s.grp_smem * gr;
-        if (sm_bytes < (size_t)warps * 32 * 8) sm_bytes = (size_t)warps * 32 * 8;
-        if (sm_bytes > 200 * 1024) continue;
-        int ps = (int)((220 * 1024) / (sm_bytes + 1024));
-        const int by_regs = MCOV_DEC_MINB * MAX_WARPS / warps; // register budget of __launch_bounds__
-        if (ps > by_regs) ps = by_regs;
-        if (ps > 16) ps = 16;
-        if (ps * gr > best) { best = ps * gr; groups = gr; per_sm = ps; }
+    int groups = per_warp, per_sm = 1;
+    if (s.st) {
+        // 7 pass warps + the store warp = 256 threads, the register budget of MCOV_DEC_MINB CTAs per SM
+        const int blk = N * env->obs_C * ow * ow * 4;
+        s.stage_pitch = round_up(blk, 128);
+        s.nbuf = s.stage_pitch * 4 <= 24 * 1024 ? 4 : 2;
+        if (env->pin_nbuf >= 2 && env->pin_nbuf <= 4) s.nbuf = env->pin_nbuf;
+        s.nsw = env->pin_sw == 2 ? 2 : 1;
+        int pw = MAX_WARPS - s.nsw;
+        for (;; --pw) {
+            groups = pw * per_warp;
+            s.bar_off = (int)(s.grp_smem * groups);
+            s.stage_off = round_up(s.bar_off + groups * 8, 128);
+            s.smem = (size_t)s.stage_off + (size_t)s.nsw * s.nbuf * s.stage_pitch;
+            if (s.smem <= 200 * 1024 || pw == 1) break;
+        }
+        s.threads = (pw + s.nsw) * 32;
+        per_sm = (int)((220 * 1024) / (s.smem + 1024));
+        const int by_regs = MCOV_DEC_MINB * MAX_WARPS / (pw + s.nsw);
+        if (per_sm > by_regs) per_sm = by_regs;
+        if (per_sm < 1) per_sm = 1;
+    } else {
+        // CTA size: the one that keeps the most lane groups resident per SM (shared memory is the limit
+        // for lidar windows: 2 x 83 kB CTAs hold 64 groups where 5 x 41 kB CTAs hold 80)
+        int best = 0;
+        for (int warps = MAX_WARPS; warps >= 1; warps >>= 1) {
+            const int gr = warps * per_warp;
+            size_t sm_bytes = s.grp_smem * gr;
+            if (sm_bytes < (size_t)warps * 32 * 8) sm_bytes = (size_t)warps * 32 * 8;
+            if (sm_bytes > 200 * 1024) continue;
+            int ps = (int)((220 * 1024) / (sm_bytes + 1024));
+            const int by_regs = MCOV_DEC_MINB * MAX_WARPS / warps; // register budget of __launch_bounds__
+            if (ps > by_regs) ps = by_regs;
+            if (ps > 16) ps = 16;
+            if (ps * gr > best) { best = ps * gr; groups = gr; per_sm = ps; }
+        }
+        s.threads = groups * s.G;
+        s.smem = s.grp_smem * groups;
     }
-    s.threads = groups * s.G;
-    s.smem = s.grp_smem * groups;
     // the statistics fold reuses the CTA's dynamic smem as blockDim doubles
     if (s.smem < (size_t)s.threads * 8) s.smem = (size_t)s.threads * 8;
     int grid = env->num_sms * per_sm;
     const int need = (c.num_envs + groups - 1) / groups;
     if (grid > need) grid = need;
+    // MCOV_DEC_GRID=n caps the grid (tests: a few CTAs looping over many envs exercise the persistent loop
+    // and the slot hand-over with small batches)
+    if (env->pin_grid >= 1 && env->pin_grid < grid) grid = env->pin_grid;
     s.grid = grid;
     return s;
 }
 
-inline uint32_t magic_for(int d) { return (uint32_t)((0x100000000ull + (uint64_t)d - 1) / (uint64_t)d); }
 
 template <class SP>
 cudaError_t launch_dec_t(mcov_env* env, const DecLaunchShape& s, const DecParams& p, cudaStream_t st) {
@@ -928,10 +1034,18 @@ cudaError_t launch_dec_t(mcov_env* env, const DecLaunchShape& s, const DecParams
 
 }  // namespace
 
-int dec_grid_size(const mcov_env* env) { return dec_shape(env).grid; }
+int dec_grid_size(const mcov_env* env) { return dec_shape(env, true).grid; }
 
 cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
-    const DecLaunchShape s = dec_shape(env);
+    if (want_dec_cta(env)) return launch_dec_cta(env, p, st);
+    const DecLaunchShape s = dec_shape(env, p.vec_ok != 0 && p.obs != nullptr && (p.phases & PH_SENSE));   // a moves-only launch writes no block
+    p.st_slot_words = s.slot_words;
+    p.st_nbuf = s.nbuf;
+    p.st_warps = s.nsw;
+    p.st_rot_div = env->pin_rot == 0 ? 0 : env->num_sms;
+    p.st_bar_off = s.bar_off;
+    p.st_stage_off = s.stage_off;
+    p.st_stage_pitch = s.stage_pitch;
     p.rad = p.ego > p.R ? p.ego : p.R;
     p.RW = 2 * p.rad + 1;
     p.bits_words = s.bits_words;
@@ -949,7 +1063,16 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     const bool c2 = plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5;
     const bool c3 = plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5;
     const bool c4 = plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5;
-    if (c2 && s.G == 4) err = launch_dec_t<Spec<4, false, 4, 2, 5>>(env, s, p, st);
+    if (s.st) {
+        if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5, true>>(env, s, p, st);
+        else if (c2 && s.G == 32) err = launch_dec_t<Spec<32, false, 4, 2, 5, true>>(env, s, p, st);
+        else if (c3 && s.G == 32) err = launch_dec_t<Spec<32, true, 8, 10, 5, true>>(env, s, p, st);
+        else if (c4 && s.G == 16) err = launch_dec_t<Spec<16, false, 16, 2, 5, true>>(env, s, p, st);
+        else if (s.G == 8) err = lidar ? launch_dec_t<Spec<8, true, 0, 0, 0, true>>(env, s, p, st) : launch_dec_t<Spec<8, false, 0, 0, 0, true>>(env, s, p, st);
+        else if (s.G == 16) err = lidar ? launch_dec_t<Spec<16, true, 0, 0, 0, true>>(env, s, p, st) : launch_dec_t<Spec<16, false, 0, 0, 0, true>>(env, s, p, st);
+        else err = lidar ? launch_dec_t<Spec<32, true, 0, 0, 0, true>>(env, s, p, st) : launch_dec_t<Spec<32, false, 0, 0, 0, true>>(env, s, p, st);
+    }
+    else if (c2 && s.G == 4) err = launch_dec_t<Spec<4, false, 4, 2, 5>>(env, s, p, st);
     else if (s.G == 4) err = lidar ? launch_dec_t<Spec<4, true, 0, 0, 0>>(env, s, p, st) : launch_dec_t<Spec<4, false, 0, 0, 0>>(env, s, p, st);
     else if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5>>(env, s, p, st);
     else if (c2 && s.G == 16) err = launch_dec_t<Spec<16, false, 4, 2, 5>>(env, s, p, st);

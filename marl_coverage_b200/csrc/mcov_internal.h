@@ -65,6 +65,12 @@ struct DecParams {
     int bits_words, grp_smem; // obs bit-stream words, shared-memory bytes per lane group
     uint32_t rw_magic, s_magic, n_magic;
     int debug;                // MCOV_DEBUG env bits (profiling aids; 0 in normal use)
+    // store-warp variant (Spec::ST, mcov_dec.cu): layout of the CTA's dynamic shared memory behind the group areas
+    int st_slot_words;        // words per bit-stream slot (two per lane group); 0 = direct stores
+    int st_nbuf;              // float32 staging buffers per store warp
+    int st_warps;             // store warps per CTA
+    int st_rot_div;           // store warp index = (blockIdx / st_rot_div) % 4 (0: the CTA's last warps)
+    int st_bar_off, st_stage_off, st_stage_pitch;
 };
 
 struct SuperParams {
@@ -164,6 +170,10 @@ struct mcov_env {
     uint64_t seed;            // seed of the last mcov_reset (auto-reset draws derive from it)
     int obs_C;
     int debug;                // MCOV_DEBUG at mcov_create (profiling aids; 0 in normal use)
+    // tuning / test pins read from the environment once, at mcov_create (-1 = not pinned):
+    // MCOV_DEC_GROUP (lanes per env), MCOV_DEC_STORE (store-warp path 0|1), MCOV_DEC_GRID (grid cap),
+    // MCOV_DEC_NBUF (staging buffers per store warp), MCOV_DEC_SW (store warps per CTA), MCOV_DEC_SHAPE (0 lane groups, 1 CTA per env), MCOV_DEC_TMA (CTA shape: 0 plain loads, 1 bulk-copy staging)
+    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma;
     size_t dec_smem_configured, super_smem_configured;   // dynamic shared memory opted into on this handle's device
     const void* dec_smem_func;  // ... and for which instantiation (MCOV_DEC_GROUP can change it between launches)
     const double* cell_values;  // Super: float64 [n_maps][W][L] reward of covering a cell, or null (= 1.0)
@@ -172,6 +182,8 @@ struct mcov_env {
 // kernel launchers (defined in the .cu files)
 namespace mcov {
 cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st);
+bool want_dec_cta(const mcov_env* env);                 // CTA-per-env shape (mcov_dec_cta.cu) instead of lane groups
+cudaError_t launch_dec_cta(mcov_env* env, DecParams& p, cudaStream_t st);
 cudaError_t launch_dec_share(mcov_env* env, cudaStream_t st);
 cudaError_t launch_dec_extras(mcov_env* env, float* obs, float* dist_term, unsigned char* scratch,
                               int pre_sense, cudaStream_t st);

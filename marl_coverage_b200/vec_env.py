@@ -390,14 +390,17 @@ class VecDecGridRL(_VecEnv):
         lay, N = self.layout, self.num_robots
         return self._hdr_field(lay.hdr_off_cov, 4 * N, torch.int32).view(self.num_envs, N)
 
-    def planes(self):
-        """(free [E,N,W,L], obst [E,N,W,L], visited [E,W,L]) boolean numpy arrays."""
+    def planes(self, envs=None):
+        """(free [E,N,W,L], obst [E,N,W,L], visited [E,W,L]) boolean numpy arrays; ``envs`` (a list of env
+        indices) restricts the unpacking to those envs, in that order."""
         lay, N, PW = self.layout, self.num_robots, self.layout.plane_words
         fo = self._plane_words(lay.off_fo, N * PW * 2).view(self.num_envs, N, PW, 2)
+        vis = self._plane_words(lay.off_visited, PW)
+        if envs is not None:
+            fo, vis = fo[list(envs)], vis[list(envs)]
         free = self._unpack(fo[..., 0].contiguous())
         obst = self._unpack(fo[..., 1].contiguous())
-        vis = self._unpack(self._plane_words(lay.off_visited, PW))
-        return free, obst, vis
+        return free, obst, self._unpack(vis)
 
 
 class VecSuperGridRL(_VecEnv):
@@ -414,9 +417,10 @@ class VecSuperGridRL(_VecEnv):
         cfg.use_scanning = int(bool(c["use_scanning"]))
         return cfg
 
-    def planes(self):
-        """(covered [E,W,L], observed_obstacles [E,W,L]) boolean numpy arrays."""
+    def planes(self, envs=None):
+        """(covered [E,W,L], observed_obstacles [E,W,L]) boolean numpy arrays; ``envs`` restricts the unpacking."""
         lay, PW = self.layout, self.layout.plane_words
-        cov = self._unpack(self._plane_words(lay.off_covered, PW))
-        seen = self._unpack(self._plane_words(lay.off_seen_obst, PW))
-        return cov, seen
+        cov, seen = self._plane_words(lay.off_covered, PW), self._plane_words(lay.off_seen_obst, PW)
+        if envs is not None:
+            cov, seen = cov[list(envs)], seen[list(envs)]
+        return self._unpack(cov), self._unpack(seen)

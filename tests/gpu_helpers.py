@@ -13,18 +13,18 @@ def vec_snapshot(vec, kind, e, reward, done, obs):
              done_thresh=float(head["done_thresh"][e].item()),
              currstep=int(head["currstep"][e].item()))
     if kind == "dec":
-        free, obst, vis = vec.planes()
+        free, obst, vis = vec.planes(envs=[e])
         s["obs"] = obs[e].cpu().numpy()
         s["adj"] = vec.adjacency()[e].astype(np.uint8)
-        s["ckpt_a"] = free[e].astype(np.uint8)
-        s["ckpt_b"] = obst[e].astype(np.uint8)
-        s["ckpt_visited"] = vis[e].astype(np.uint8)
+        s["ckpt_a"] = free[0].astype(np.uint8)
+        s["ckpt_b"] = obst[0].astype(np.uint8)
+        s["ckpt_visited"] = vis[0].astype(np.uint8)
     else:
-        cov, seen = vec.planes()
+        cov, seen = vec.planes(envs=[e])
         st = obs[e].cpu().numpy()
         s["state_crc"] = crc_f32(st)
-        s["ckpt_a"] = cov[e].astype(np.uint8)
-        s["ckpt_b"] = seen[e].astype(np.uint8)
+        s["ckpt_a"] = cov[0].astype(np.uint8)
+        s["ckpt_b"] = seen[0].astype(np.uint8)
         s["ckpt_state"] = st
     return s
 

@@ -47,6 +47,40 @@ def test_dec_golden_every_group_width(name, group, monkeypatch):
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=37, check_envs=(0, 36))
 
 
+@pytest.mark.parametrize("name,group,store", [(n, g, 1) for n in ("dec_c2_square_100", "dec_lidar_21x10_100",
+                                                                   "dec_mapsharing_comm12", "dec_dist_reward_15")
+                                              for g in (8, 16, 32)] + [("dec_c2_square_100", 8, 0)])
+def test_dec_golden_store_warp(name, group, store, monkeypatch):
+    """Large batches hand their observation blocks to a store warp (bit-stream slots, mbarriers, TMA bulk
+    stores); small ones store directly.  Both paths must give the same bits (MCOV_DEC_STORE pins the path).
+    Two CTAs loop over 150 envs, so every lane group reuses both of its slots several times (the one
+    store = 0 case runs the same capped grid through the direct stores)."""
+    from marl_coverage_b200 import VecDecGridRL
+    from gpu_helpers import replay_trace_on_gpu
+    monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
+    monkeypatch.setenv("MCOV_DEC_STORE", str(store))
+    monkeypatch.setenv("MCOV_DEC_GRID", "2")
+    tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    replay_trace_on_gpu(tr, VecDecGridRL, num_envs=150, check_envs=(0, 61, 149))
+
+
+@pytest.mark.parametrize("tma", [0, 1])
+@pytest.mark.parametrize("name", DEC_TRACES)
+def test_dec_golden_cta_per_env_shape(name, tma, monkeypatch):
+    """Small batches / large maps run one CTA per env (warp per robot, lane per band row; mcov_dec_cta.cu), with
+    the map windows staged into shared memory by bulk async copies (tma = 1) or read with plain loads (tma = 0).
+    Every golden trace must give the same bits as through the lane-group kernel (MCOV_DEC_SHAPE pins the shape).
+    Three CTAs loop over seven envs."""
+    from marl_coverage_b200 import VecDecGridRL
+    from gpu_helpers import replay_trace_on_gpu
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "1")
+    monkeypatch.setenv("MCOV_DEC_TMA", str(tma))
+    monkeypatch.setenv("MCOV_DEC_GRID", "3")
+    tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    tol = 1e-6 if tr.config["mini_map_rad"] > 0 else 0.0
+    replay_trace_on_gpu(tr, VecDecGridRL, num_envs=7, check_envs=(0, 6), obs_tol=tol)
+
+
 @pytest.mark.parametrize("name", [n for n in DEC_TRACES if "lidar" in n])
 def test_dec_lidar_float64_march_path(name, monkeypatch):
     """The lidar normally walks an integer beam table proved exact on the host; the float64 DDA

@@ -147,6 +147,27 @@ def test_dec_random_vs_oracle(seed):
     _run_case("dec", 1000 + seed)
 
 
+@pytest.mark.parametrize("seed", range(16))
+def test_dec_random_vs_oracle_store_warp(seed, monkeypatch):
+    """Same cases through the store-warp path (slot hand-over + TMA bulk stores), one CTA looping over the
+    batch: masked resets publish empty slots, generic shapes fall back to direct stores when the block is
+    not a 16-byte multiple."""
+    monkeypatch.setenv("MCOV_DEC_STORE", "1")
+    monkeypatch.setenv("MCOV_DEC_GRID", "1")
+    _run_case("dec", 1000 + seed, E=70)
+
+
+@pytest.mark.parametrize("tma", [0, 1])
+@pytest.mark.parametrize("seed", range(20))
+def test_dec_random_vs_oracle_cta_shape(seed, tma, monkeypatch):
+    """Same cases through the CTA-per-env kernel (auto-selected for small batches; pinned here), with and
+    without bulk-copy staging of the map windows: odd map sizes put the staged runs at every alignment."""
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "1")
+    monkeypatch.setenv("MCOV_DEC_TMA", str(tma))
+    monkeypatch.setenv("MCOV_DEC_GRID", "4")
+    _run_case("dec", 1000 + seed)
+
+
 @pytest.mark.parametrize("seed", range(24))
 def test_super_random_vs_oracle(seed):
     _run_case("super", 2000 + seed)
@@ -184,6 +205,15 @@ def test_whole_parameter_range_vs_oracle(kind, k):
 
 @pytest.mark.parametrize("case", range(len(EDGE)))
 def test_limits_and_degenerate_shapes_vs_oracle(case):
+    kind, force = EDGE[case]
+    _run_case(kind, 7000 + case, E=3, T=25, force=force)
+
+
+@pytest.mark.parametrize("case", [k for k in range(len(EDGE)) if EDGE[k][0] == "dec"])
+def test_limits_and_degenerate_shapes_cta_shape(case, monkeypatch):
+    """The same limits (32 robots = 32 warps, radius 15 = 31-row bands, 1023 lasers, 5 x 6 maps) through the
+    CTA-per-env kernel."""
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "1")
     kind, force = EDGE[case]
     _run_case(kind, 7000 + case, E=3, T=25, force=force)
 

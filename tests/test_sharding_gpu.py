@@ -45,3 +45,36 @@ def test_logical_shards_equal_single_batch(shards):
     idx = [0, 1, 2, 4, 5, 6]                              # integer-valued sums: exact in any order
     assert np.array_equal(tot_whole[idx], tot_parts[idx])
     assert np.allclose(tot_whole[3], tot_parts[3], rtol=1e-12)   # coverage fractions: order of summation differs
+
+
+@pytest.mark.parametrize("group", [8, 32])
+def test_store_warp_equals_direct_stores_with_auto_reset(group, monkeypatch):
+    """The store-warp path (bit-stream slots -> TMA bulk stores) against the direct-store path on the same
+    seeded batch with fused auto-resets: a finished env re-runs its pass in RESET mode before its slot is
+    published.  One CTA loops over the batch, so slots are reused many times."""
+    import torch
+    from marl_coverage_b200 import VecDecGridRL, load_grid_set
+    grids = load_grid_set("bg2_100x100", 6)
+    E, N, T = 301, 4, 90
+    g = torch.Generator(device="cuda")
+    g.manual_seed(8)
+    acts = torch.randint(0, 4, (T, E, N), dtype=torch.uint8, device="cuda", generator=g)
+    monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
+    monkeypatch.setenv("MCOV_DEC_GRID", "3")
+    envs = []
+    for store in (0, 1):
+        monkeypatch.setenv("MCOV_DEC_STORE", str(store))           # read once, at mcov_create
+        envs.append(VecDecGridRL(grids, CFG, num_envs=E, auto_reset=True, truncate_steps=40, seed=5))
+    a, b = envs
+    assert torch.equal(a.reset(), b.reset())
+    episodes = 0.0
+    for t in range(T):
+        oa, ra, da = a.step(acts[t], want_stats=True)
+        ob, rb, db = b.step(acts[t], want_stats=True)
+        assert torch.equal(oa, ob) and torch.equal(da, db) and torch.equal(a.reward64, b.reward64), "step %d" % t
+        sa, sb = a.stats.cpu().numpy(), b.stats.cpu().numpy()
+        assert np.array_equal(sa[[0, 2, 4, 5, 6]], sb[[0, 2, 4, 5, 6]]) and np.allclose(sa, sb, rtol=1e-12)   # float sums: group order differs
+        episodes += float(a.stats[0].item())
+    assert episodes > 0
+    fa, fb = a.planes(), b.planes()
+    assert all(np.array_equal(x, y) for x, y in zip(fa, fb))
