@@ -301,6 +301,7 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
     e->pin_sw = pin("MCOV_DEC_SW");
     e->pin_rot = pin("MCOV_DEC_ROT");
     e->pin_tma = pin("MCOV_DEC_TMA");
+    e->pin_team = pin("MCOV_DEC_TEAM");
     *out = e;
     return MCOV_OK;
 }

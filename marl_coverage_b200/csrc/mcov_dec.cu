@@ -111,6 +111,17 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
     return s;
 }
 
+#ifndef MCOV_ST_UNROLL
+#define MCOV_ST_UNROLL 4                     // unroll of the observation store loop
+#endif
+#define MCOV_PRAGMA_(x) _Pragma(#x)
+#define MCOV_UNROLL(n) MCOV_PRAGMA_(unroll n)
+#ifndef MCOV_LIDAR_PERM
+#define MCOV_LIDAR_PERM 0                    // beam table walk: spread the beams a warp walks at once over the circle (A/B on C3: 0.1019 vs 0.1022 ms, noise; off)
+#endif
+#ifndef MCOV_LIDAR_RUNS
+#define MCOV_LIDAR_RUNS 0                    // beam table walk: one shared-memory atomic per same-row run of cells (A/B on C3: 0.1108 vs 0.1022 ms, slower; off)
+#endif
 #ifndef MCOV_PF_NEXT
 #define MCOV_PF_NEXT 0                       // measured on B200 (C5): 0.213 -> 0.233 ms with it on — the step is DRAM-throughput bound, extra line fetches cost more than the latency they hide
 #endif
@@ -395,7 +406,15 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 for (int idx = lg; idx < N * nl; idx += G) {
                     // neighbouring lanes take the same beam of different robots: beams of one robot share
                     // cells near the origin and would collide on the same shared-memory words
-                    const int l = div_n(idx), i = idx - l * N;
+                    const int l0 = div_n(idx), i = idx - l0 * N;
+#if MCOV_LIDAR_PERM
+                    // ... and the 32/N beams a warp walks at once are spread over the circle (l -> l * m mod n_lasers,
+                    // m ~ n_lasers / 4 coprime to it): adjacent beams run through the same cells for their first steps
+                    const int lm = l0 * (int)p.l_mult;
+                    const int l = lm - nl * fast_div(lm, p.l_magic);
+#else
+                    const int l = l0;
+#endif
                     const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
                     const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
                     const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
@@ -403,6 +422,25 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     uint32_t* wf = sm.winF + i * S;
                     uint32_t* wo = sm.winO + i * S;
                     if ((ww[R] >> R) & 1u) continue;               // own cell is an obstacle: the beam ended there
+#if MCOV_LIDAR_RUNS
+                    // consecutive cells of a beam that stay in one window row are ORed in with one atomic
+                    int run_rx = R;
+                    uint32_t run = 0;
+#pragma unroll
+                    for (int k = 1; k < 16; ++k) {
+                        const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
+                        if (cell == 0xffffu) break;
+                        const int rx = (int)(cell & 0xffu), ry = (int)(cell >> 8);
+                        if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
+                        if (rx != run_rx) {
+                            if (run) atomicOr(&wf[run_rx], run);
+                            run_rx = rx;
+                            run = 0;
+                        }
+                        run |= 1u << ry;
+                    }
+                    if (run) atomicOr(&wf[run_rx], run);
+#else
 #pragma unroll
                     for (int k = 1; k < 16; ++k) {
                         const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
@@ -411,6 +449,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                         if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
                         atomicOr(&wf[rx], 1u << ry);
                     }
+#endif
                 }
             } else {
             const double rng = (double)R;
@@ -652,13 +691,14 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
         return PASS_DONE;
     }
     if (p.debug & 1) return PASS_DONE;                             // MCOV_DEBUG=1: profiling aid, no obs store
+    if (p.store_team > G) return PASS_STORE;                       // the block is stored by the group's team (kernel loop)
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
         const int nf4 = p.obs_env_floats >> 2;
         // float4 q = lg + G*t holds bits [4q, 4q+4): word q>>3, nibble q&7
         float4* d = dst + lg;
         const int iters = (nf4 - lg + G - 1) / G;
-#pragma unroll 4
+MCOV_UNROLL(MCOV_ST_UNROLL)
         for (int t = 0; t < iters; ++t) {
             const int q = lg + t * G;
             obs_store(d + t * G, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
@@ -716,28 +756,36 @@ dec_env_kernel(const DecParams p) {
     Prefetch nxt;
     nxt.pos = 0; nxt.act8 = 0; nxt.act64 = 0; nxt.map_idx = 0; nxt.shown = 0;
     if (mode != MODE_RESET && gg < p.E) nxt = load_prefetch(p, gg, g.lg);
-    for (int e = gg; e < p.E; e += gtot) {
+    // Store teams (p.store_team = T > G lanes, a power of two <= 32): the T / G lane groups of a team run their
+    // passes side by side, then all T lanes store the team's blocks one after the other — a block leaves in
+    // 16 T-byte pieces instead of 16 G-byte ones (8 -> 16 lanes: tools/ubench/store_patterns.cu 4.65 -> 5.4 TB/s).
+    // The loop is team-uniform: a group without an env (tail of the batch, masked reset) still meets its team.
+    const int T = (!SP::ST && p.store_team > G) ? p.store_team : G;
+    const int gpt = T / G, tpos = gi & (gpt - 1);                  // groups per team, this group's place in it
+    const int lane = threadIdx.x & 31, tbase = lane & ~(T - 1);
+    const unsigned tmask = T == 32 ? FULL : (((1u << (T & 31)) - 1u) << tbase);
+    for (int e0 = gg - tpos; e0 < p.E; e0 += gtot) {
+        const int e = e0 + tpos;
+        int has_block = 0;
+        if (e < p.E) {
         const Prefetch cur = nxt;
         if (mode != MODE_RESET && e + gtot < p.E) nxt = load_prefetch(p, e + gtot, g.lg);
         int m = mode;
         if (SP::ST) sm.bits = bits0 + (link.it & 1) * p.st_slot_words;
+        bool act = true;
         if (m == MODE_RESET) {
-            int act = 1;
-            if (p.mask) act = p.mask[e];
-            else if (p.mask_from_flags) act = p.needs_reset[e];
-            if (!act) {                                            // group-uniform
-                if (SP::ST) {                                      // the store warp counts slots: publish an empty one
-                    wait_slot_free(link);
-                    if (g.lg == 0) {
-                        sm.bits[p.bits_words] = 0xffffffffu;
-                        st_release_smem(link.pub, (uint32_t)link.it + 1u);
-                    }
-                    ++link.it;
+            if (p.mask) act = p.mask[e] != 0;
+            else if (p.mask_from_flags) act = p.needs_reset[e] != 0;
+            if (!act && SP::ST) {                                  // group-uniform; the store warp counts slots: publish an empty one
+                wait_slot_free(link);
+                if (g.lg == 0) {
+                    sm.bits[p.bits_words] = 0xffffffffu;
+                    st_release_smem(link.pub, (uint32_t)link.it + 1u);
                 }
-                continue;
+                ++link.it;
             }
         }
-        if (!SP::ST && (p.debug & 2)) {                            // MCOV_DEBUG=2: profiling aid, obs store only
+        if (act && !SP::ST && (p.debug & 2)) {                     // MCOV_DEBUG=2: profiling aid, obs store only
             float4* d = reinterpret_cast<float4*>(p.obs + (size_t)e * p.obs_env_floats) + g.lg;
             const int iters = ((p.obs_env_floats >> 2) - g.lg + G - 1) / G;
 #pragma unroll 4
@@ -745,11 +793,29 @@ dec_env_kernel(const DecParams p) {
                 const int q = g.lg + t * G;
                 obs_store(d + t * G, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
             }
-            continue;
+        } else if (act) {
+            const int e_next = (mode == MODE_STEP && e + gtot < p.E) ? e + gtot : -1;
+            int r;
+            while ((r = env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next, link)) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
+            has_block = (r == PASS_STORE);
+            ++link.it;
         }
-        const int e_next = (mode == MODE_STEP && e + gtot < p.E) ? e + gtot : -1;
-        while (env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next, link) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
-        ++link.it;
+        }
+        if (T > G) {
+            __syncwarp(tmask);                                     // the team's bit streams are complete
+            const unsigned hb = __ballot_sync(tmask, has_block && g.lg == 0);
+            const int tl = lane & (T - 1), nf4 = p.obs_env_floats >> 2;
+            for (int b = 0; b < gpt; ++b) {
+                if (!((hb >> (tbase + b * G)) & 1u)) continue;     // team-uniform
+                const uint32_t* bb = reinterpret_cast<const uint32_t*>(smem_raw + (size_t)(gi - tpos + b) * p.grp_smem +
+                                                                       MCOV_STATS_LEN * 8);
+                float4* d = reinterpret_cast<float4*>(p.obs + (size_t)(e0 + b) * p.obs_env_floats);
+MCOV_UNROLL(MCOV_ST_UNROLL)
+                for (int q = tl; q < nf4; q += T)
+                    obs_store(d + q, lut[(bb[q >> 3] >> ((q & 7) * 4)) & 15u]);
+            }
+            __syncwarp(tmask);                                     // ... and read out before the next pass clears them
+        }
     }
     } else {
         // ---- store warp: full slot -> float32 staging buffer -> one TMA bulk store per env block ----
@@ -906,6 +972,7 @@ struct DecLaunchShape {
     int bits_words;
     // store-warp variant (Spec::ST): 0 = off
     int st, slot_words, nbuf, bar_off, stage_off, stage_pitch, nsw;
+    int team;                 // lanes that store a block together (>= G)
 };
 
 inline int pick_group(const mcov_env* env) {
@@ -918,12 +985,12 @@ inline int pick_group(const mcov_env* env) {
     int g = 8;
     if (c.num_robots > 16) g = 32;
     else if (c.num_robots > 8) g = 16;
-    // heavy envs (many robots x tall windows, e.g. 8 robots x 21-row lidar windows = 168 window rows)
-    // get more lanes so that the row loop stays at <= 6 iterations: measured on C3, 8 -> 32 lanes
-    // takes the step from 0.160 to 0.111 ms
+    // the row loop of the band (robots x (2*rad+1) rows) should stay at <= 3 iterations: measured on B200
+    // (profiles/r02_ab.jsonl), C5 (4 robots x 11 rows) 8 -> 16 lanes takes the step from 0.214 to 0.196 ms
+    // (32 lanes: 0.226), C3 (8 robots x 21-row lidar bands) 8 -> 32 lanes from 0.160 to 0.111 ms
     const int rad = c.egoradius > c.sensor_range ? c.egoradius : c.sensor_range;
     const int rows = c.num_robots * (2 * rad + 1);
-    while (g < 32 && rows > 6 * g) g *= 2;
+    while (g < 32 && rows > 3 * g) g *= 2;
     const long long capacity = (long long)num_sms * 4 * MAX_WARPS * 32;      // resident threads
     while (g < 32 && (long long)c.num_envs * (2 * g) <= capacity) g *= 2;
     // MCOV_DEC_GROUP=8|16|32 pins the width (tests run every width on the same traces; tuning)
@@ -1002,6 +1069,10 @@ inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
         s.threads = groups * s.G;
         s.smem = s.grp_smem * groups;
     }
+    // store teams: MCOV_DEC_TEAM=8|16|32 pins the lanes per block store (>= G; needs the vector path)
+    s.team = s.G;
+    if (!s.st && vec_ok && env->pin_team > s.G && env->pin_team <= 32 && (env->pin_team & (env->pin_team - 1)) == 0 &&
+        groups % (env->pin_team / s.G) == 0) s.team = env->pin_team;
     // the statistics fold reuses the CTA's dynamic smem as blockDim doubles
     if (s.smem < (size_t)s.threads * 8) s.smem = (size_t)s.threads * 8;
     int grid = env->num_sms * per_sm;
@@ -1043,6 +1114,7 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.st_nbuf = s.nbuf;
     p.st_warps = s.nsw;
     p.st_rot_div = env->pin_rot == 0 ? 0 : env->num_sms;
+    p.store_team = s.team;
     p.st_bar_off = s.bar_off;
     p.st_stage_off = s.stage_off;
     p.st_stage_pitch = s.stage_pitch;
@@ -1054,6 +1126,14 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.s_magic = magic_for(p.S);
     p.n_magic = magic_for(p.N);
     p.l_magic = magic_for(p.n_lasers > 0 ? p.n_lasers : 1);
+    {
+        const int nl = p.n_lasers > 0 ? p.n_lasers : 1;
+        auto gcd = [](int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; };
+        int m = nl / 4 + 1;
+        while (gcd(m, nl) != 1) ++m;
+        p.l_mult = (uint32_t)(m % nl);
+        if (nl == 1) p.l_mult = 0;
+    }
     const bool lidar = p.sensor == MCOV_SENSOR_LIDAR;
     p.debug = env->debug;                                           // MCOV_DEBUG, read once at mcov_create
     if ((uint64_t)p.E * p.N * p.g.PW >= 0xffffffffull) return cudaErrorInvalidValue;   // 32-bit word offsets

@@ -9,7 +9,7 @@ namespace mcov {
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
-enum { PASS_DONE = 0, PASS_AGAIN = 2 };   // env pass results (PASS_AGAIN: re-seed the finished env in place)
+enum { PASS_DONE = 0, PASS_STORE = 1, PASS_AGAIN = 2 };   // env pass results (PASS_STORE: the caller stores the block; PASS_AGAIN: re-seed the finished env in place)
 
 // floor(k / d) for k < 2^26, d <= 64, magic = ceil(2^32 / d)
 // (d == 1 gives magic = 2^32 = 0 in 32 bits: the quotient is k itself)

@@ -23,6 +23,7 @@ struct DecParams {
     const double* beams;      // [n_lasers][3] device
     const uint16_t* lidar_cells;  // [n_lasers][16] window cells of each beam in march order (0xffff ends), or null
     uint32_t l_magic;         // ceil(2^32 / n_lasers)
+    uint32_t l_mult;          // beam permutation of the table walk: l -> l * l_mult mod n_lasers (coprime)
     int single_tool, comm_radius, want_adj, dist_reward;
     int maxsteps, truncate_steps, auto_reset;
     int env_id_base;
@@ -69,6 +70,7 @@ struct DecParams {
     int st_slot_words;        // words per bit-stream slot (two per lane group); 0 = direct stores
     int st_nbuf;              // float32 staging buffers per store warp
     int st_warps;             // store warps per CTA
+    int store_team;           // lanes that store an observation block together (>= lanes per env; direct-store path)
     int st_rot_div;           // store warp index = (blockIdx / st_rot_div) % 4 (0: the CTA's last warps)
     int st_bar_off, st_stage_off, st_stage_pitch;
 };
@@ -173,7 +175,7 @@ struct mcov_env {
     // tuning / test pins read from the environment once, at mcov_create (-1 = not pinned):
     // MCOV_DEC_GROUP (lanes per env), MCOV_DEC_STORE (store-warp path 0|1), MCOV_DEC_GRID (grid cap),
     // MCOV_DEC_NBUF (staging buffers per store warp), MCOV_DEC_SW (store warps per CTA), MCOV_DEC_SHAPE (0 lane groups, 1 CTA per env), MCOV_DEC_TMA (CTA shape: 0 plain loads, 1 bulk-copy staging)
-    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma;
+    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma, pin_team;
     size_t dec_smem_configured, super_smem_configured;   // dynamic shared memory opted into on this handle's device
     const void* dec_smem_func;  // ... and for which instantiation (MCOV_DEC_GROUP can change it between launches)
     const double* cell_values;  // Super: float64 [n_maps][W][L] reward of covering a cell, or null (= 1.0)

@@ -43,6 +43,7 @@ def test_dec_golden_every_group_width(name, group, monkeypatch):
     from marl_coverage_b200 import VecDecGridRL
     from gpu_helpers import replay_trace_on_gpu
     monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "0")
     tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=37, check_envs=(0, 36))
 
@@ -57,9 +58,26 @@ def test_dec_golden_store_warp(name, group, store, monkeypatch):
     store = 0 case runs the same capped grid through the direct stores)."""
     from marl_coverage_b200 import VecDecGridRL
     from gpu_helpers import replay_trace_on_gpu
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "0")
     monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
     monkeypatch.setenv("MCOV_DEC_STORE", str(store))
     monkeypatch.setenv("MCOV_DEC_GRID", "2")
+    tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    replay_trace_on_gpu(tr, VecDecGridRL, num_envs=150, check_envs=(0, 61, 149))
+
+
+@pytest.mark.parametrize("group,team", [(8, 16), (8, 32), (16, 32)])
+@pytest.mark.parametrize("name", ["dec_c2_square_100", "dec_lidar_21x10_100", "dec_mapsharing_comm12",
+                                  "dec_dist_reward_15"])
+def test_dec_golden_store_teams(name, group, team, monkeypatch):
+    """Two or four lane groups store their observation blocks together, 16 / 32 lanes per block (MCOV_DEC_TEAM pins
+    the team; the kernel picks it from the shape).  Two CTAs loop over 150 envs: the last teams are incomplete."""
+    from marl_coverage_b200 import VecDecGridRL
+    from gpu_helpers import replay_trace_on_gpu
+    monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
+    monkeypatch.setenv("MCOV_DEC_TEAM", str(team))
+    monkeypatch.setenv("MCOV_DEC_GRID", "2")
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "0")
     tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=150, check_envs=(0, 61, 149))
 

@@ -152,6 +152,7 @@ def test_dec_random_vs_oracle_store_warp(seed, monkeypatch):
     """Same cases through the store-warp path (slot hand-over + TMA bulk stores), one CTA looping over the
     batch: masked resets publish empty slots, generic shapes fall back to direct stores when the block is
     not a 16-byte multiple."""
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "0")
     monkeypatch.setenv("MCOV_DEC_STORE", "1")
     monkeypatch.setenv("MCOV_DEC_GRID", "1")
     _run_case("dec", 1000 + seed, E=70)

@@ -47,11 +47,13 @@ def test_logical_shards_equal_single_batch(shards):
     assert np.allclose(tot_whole[3], tot_parts[3], rtol=1e-12)   # coverage fractions: order of summation differs
 
 
-@pytest.mark.parametrize("group", [8, 32])
-def test_store_warp_equals_direct_stores_with_auto_reset(group, monkeypatch):
-    """The store-warp path (bit-stream slots -> TMA bulk stores) against the direct-store path on the same
-    seeded batch with fused auto-resets: a finished env re-runs its pass in RESET mode before its slot is
-    published.  One CTA loops over the batch, so slots are reused many times."""
+@pytest.mark.parametrize("group,variant", [(8, "MCOV_DEC_STORE=1"), (32, "MCOV_DEC_STORE=1"), (8, "MCOV_DEC_TEAM=16"),
+                                           (8, "MCOV_DEC_TEAM=32"), (16, "MCOV_DEC_TEAM=32"), (8, "MCOV_DEC_SHAPE=1")])
+def test_kernel_variants_equal_plain_path_with_auto_reset(group, variant, monkeypatch):
+    """The variants of the DecGridRL step kernel — store warp (bit-stream slots -> TMA bulk stores), store teams
+    (16 / 32 lanes write a block together), CTA-per-env shape — against the plain lane-group path on the same seeded
+    batch with fused auto-resets: a finished env re-runs its pass in RESET mode before its block is written.  Three
+    CTAs loop over the batch (slots and teams are reused many times; the batch size leaves some teams incomplete)."""
     import torch
     from marl_coverage_b200 import VecDecGridRL, load_grid_set
     grids = load_grid_set("bg2_100x100", 6)
@@ -61,9 +63,12 @@ def test_store_warp_equals_direct_stores_with_auto_reset(group, monkeypatch):
     acts = torch.randint(0, 4, (T, E, N), dtype=torch.uint8, device="cuda", generator=g)
     monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
     monkeypatch.setenv("MCOV_DEC_GRID", "3")
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "0")
     envs = []
-    for store in (0, 1):
-        monkeypatch.setenv("MCOV_DEC_STORE", str(store))           # read once, at mcov_create
+    for on in (False, True):                                        # pins are read once, at mcov_create
+        if on:
+            k, v = variant.split("=")
+            monkeypatch.setenv(k, v)
         envs.append(VecDecGridRL(grids, CFG, num_envs=E, auto_reset=True, truncate_steps=40, seed=5))
     a, b = envs
     assert torch.equal(a.reset(), b.reset())
