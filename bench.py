@@ -714,7 +714,7 @@ def run_gpu(args):
         others = {}
         del env, res, act_dev
         torch.cuda.empty_cache()
-        for wl in ("c2", "c3", "c4", "super"):
+        for wl in ("c2", "c3", "c4", "super", "c2_share", "c2_dist", "c2_dijkstra"):
             try:
                 others[wl] = workload_summary(torch, wl, device, flush_buf)
             except Exception as ex:
