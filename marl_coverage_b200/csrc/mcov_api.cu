@@ -177,6 +177,7 @@ void fill_dec_params(mcov_env* env, mcov::DecParams& p) {
     p.n_lasers = c.num_lasers;
     p.beams = env->beams_dev;
     p.lidar_cells = env->lidar_cells_dev;
+    p.lidar_runs = env->lidar_runs_dev;
     p.single_tool = c.single_square_tool;
     p.comm_radius = c.comm_radius;
     p.want_adj = 1;
@@ -302,6 +303,7 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
     e->pin_rot = pin("MCOV_DEC_ROT");
     e->pin_tma = pin("MCOV_DEC_TMA");
     e->pin_team = pin("MCOV_DEC_TEAM");
+    e->pin_warps = pin("MCOV_DEC_WARPS");
     *out = e;
     return MCOV_OK;
 }
@@ -310,6 +312,7 @@ int mcov_destroy(mcov_env* env) {
     if (!env) return MCOV_OK;
     if (env->beams_dev) cudaFree(env->beams_dev);
     if (env->lidar_cells_dev) cudaFree(env->lidar_cells_dev);
+    if (env->lidar_runs_dev) cudaFree(env->lidar_runs_dev);
     delete env;
     return MCOV_OK;
 }
@@ -332,6 +335,7 @@ int mcov_set_lidar_beams(mcov_env* env, const double* beams_host, int num_lasers
     // increment is itself an integer: exact arithmetic) the visited cells are start + floor(k*inc)
     // for EVERY start, and the march becomes a table walk.  Otherwise the float64 march stays.
     if (env->lidar_cells_dev) { cudaFree(env->lidar_cells_dev); env->lidar_cells_dev = nullptr; }
+    if (env->lidar_runs_dev) { cudaFree(env->lidar_runs_dev); env->lidar_runs_dev = nullptr; }
     const int R = env->cfg.sensor_range;
     const char* force = getenv("MCOV_LIDAR_FP64");
     bool ok = !(force && atoi(force) != 0);
@@ -358,12 +362,41 @@ int mcov_set_lidar_beams(mcov_env* env, const double* beams_host, int num_lasers
         }
         for (int j = k + 1; ok && j < 16; ++j) table[l * 16 + j] = 0xffffu;
     }
+    // The same cells grouped into same-row runs (what the kernels walk): consecutive cells of a beam that stay in one
+    // window row become one {mask, row} entry; inside a run y moves strictly one way, so the first wall of the run is
+    // the lowest (or highest) set bit of wall & mask and the free cells before it are one more mask.
+    uint2* runs = ok ? new (std::nothrow) uint2[(size_t)num_lasers * 16] : nullptr;
+    if (ok && !runs) ok = false;
+    for (int l = 0; ok && l < num_lasers; ++l) {
+        const uint16_t* c = table + (size_t)l * 16;
+        int nr = 0, k = 1;
+        while (ok && k < 16 && c[k] != 0xffffu) {
+            const int rx = c[k] & 0xff;
+            int prev = c[k] >> 8, dir = 0;
+            uint32_t mask = 1u << prev;
+            for (++k; k < 16 && c[k] != 0xffffu && (c[k] & 0xff) == rx; ++k) {
+                const int ry = c[k] >> 8;
+                const int d = ry > prev ? 1 : (ry < prev ? -1 : 0);
+                if (d == 0 || (dir != 0 && d != dir)) { ok = false; break; }   // not monotone: keep the float64 march
+                dir = d;
+                mask |= 1u << ry;
+                prev = ry;
+            }
+            if (nr >= 15) ok = false;
+            if (ok) runs[(size_t)l * 16 + nr++] = make_uint2(mask, (uint32_t)(rx * 4) | (dir < 0 ? 0x80000000u : 0u));
+        }
+        for (int j = nr; ok && j < 16; ++j) runs[(size_t)l * 16 + j] = make_uint2(0u, 0u);
+    }
     if (ok) {
         ce = cudaMalloc(&env->lidar_cells_dev, sizeof(uint16_t) * 16 * num_lasers);
         if (ce == cudaSuccess)
             ce = cudaMemcpy(env->lidar_cells_dev, table, sizeof(uint16_t) * 16 * num_lasers, cudaMemcpyHostToDevice);
-        if (ce != cudaSuccess) { delete[] table; return cuda_fail(ce, "cudaMalloc/cudaMemcpy(lidar cells)"); }
+        if (ce == cudaSuccess) ce = cudaMalloc(&env->lidar_runs_dev, sizeof(uint2) * 16 * num_lasers);
+        if (ce == cudaSuccess)
+            ce = cudaMemcpy(env->lidar_runs_dev, runs, sizeof(uint2) * 16 * num_lasers, cudaMemcpyHostToDevice);
+        if (ce != cudaSuccess) { delete[] table; delete[] runs; return cuda_fail(ce, "cudaMalloc/cudaMemcpy(lidar cells)"); }
     }
+    delete[] runs;
     delete[] table;
     return MCOV_OK;
 }

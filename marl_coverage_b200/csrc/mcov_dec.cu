@@ -116,6 +116,16 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
 #endif
 #define MCOV_PRAGMA_(x) _Pragma(#x)
 #define MCOV_UNROLL(n) MCOV_PRAGMA_(unroll n)
+#ifndef MCOV_LUT8
+#define MCOV_LUT8 0                          // observation store: byte -> 2 x float4 table (8 kB of shared memory per CTA)
+#endif
+#ifndef MCOV_NO_PF
+#define MCOV_NO_PF 0                         // 1: drop the L1 prefetch of the window runs before the band-row loop
+#endif
+#ifndef MCOV_LIDAR_RUNTAB
+#define MCOV_LIDAR_RUNTAB 0                  // 1: beam table walk over host-built same-row runs — parity-green, A/B on C3: 0.129 vs 0.104 ms
+                                             // cell by cell (a warp's beams have 1..10 runs: the longest decides, and a run costs more than a cell)
+#endif
 #ifndef MCOV_LIDAR_PERM
 #define MCOV_LIDAR_PERM 0                    // beam table walk: spread the beams a warp walks at once over the circle (A/B on C3: 0.1019 vs 0.1022 ms, noise; off)
 #endif
@@ -202,7 +212,7 @@ __device__ __forceinline__ void prefetch_next_env(const DecParams& p, const Pref
 
 
 template <class SP>
-__device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut,
+__device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm, const float4* lut, const float4* lut8,
                                          const int e, const int mode, const Prefetch& cur,
                                          const Grp<SP::G>& g, const Prefetch& nxt, const int e_next,
                                          const StoreLink& link) {
@@ -345,7 +355,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     g.sync();
 
     const bool do_sense = fresh || (mode == MODE_STEP && !sentinel);
-    if (!fresh) {
+    if (!fresh && !MCOV_NO_PF) {
         // Pull the lines under every robot's window towards the SM now: band rows are contiguous in
         // x within a strip ((2*rad+1) * 8 B <= 2 lines), so touching the first and last row of each
         // run covers it.  One lane per (robot, strip); the slot loop below then hits L1/L2 instead
@@ -415,32 +425,16 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
 #else
                     const int l = l0;
 #endif
-                    const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
-                    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
-                    const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
                     const uint32_t* ww = sm.wallW + i * S;
                     uint32_t* wf = sm.winF + i * S;
                     uint32_t* wo = sm.winO + i * S;
                     if ((ww[R] >> R) & 1u) continue;               // own cell is an obstacle: the beam ended there
-#if MCOV_LIDAR_RUNS
-                    // consecutive cells of a beam that stay in one window row are ORed in with one atomic
-                    int run_rx = R;
-                    uint32_t run = 0;
-#pragma unroll
-                    for (int k = 1; k < 16; ++k) {
-                        const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
-                        if (cell == 0xffffu) break;
-                        const int rx = (int)(cell & 0xffu), ry = (int)(cell >> 8);
-                        if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
-                        if (rx != run_rx) {
-                            if (run) atomicOr(&wf[run_rx], run);
-                            run_rx = rx;
-                            run = 0;
-                        }
-                        run |= 1u << ry;
-                    }
-                    if (run) atomicOr(&wf[run_rx], run);
+#if MCOV_LIDAR_RUNTAB
+                    walk_beam_runs(p.lidar_runs, l, ww, wf, wo);
 #else
+                    const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
+                    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
+                    const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
 #pragma unroll
                     for (int k = 1; k < 16; ++k) {
                         const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
@@ -695,6 +689,27 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
         const int nf4 = p.obs_env_floats >> 2;
+#if MCOV_LUT8
+        // one byte of the bit stream -> two float4 through a 256-entry table: 4 instead of 7 instructions per float4
+        {
+            const int np = nf4 >> 1;
+            float4* d2 = dst + 2 * lg;
+            const int it2 = (np - lg + G - 1) / G;
+MCOV_UNROLL(MCOV_ST_UNROLL)
+            for (int t = 0; t < it2; ++t) {
+                const int pq = lg + t * G;
+                const uint32_t byte = (sm.bits[pq >> 2] >> ((pq & 3) * 8)) & 255u;
+                const float4 v0 = lut8[2 * byte], v1 = lut8[2 * byte + 1];
+                obs_store(d2 + 2 * t * G, v0);
+                obs_store(d2 + 2 * t * G + 1, v1);
+            }
+            if ((nf4 & 1) && lg == 0) {
+                const int q = nf4 - 1;
+                obs_store(dst + q, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
+            }
+            return PASS_DONE;
+        }
+#endif
         // float4 q = lg + G*t holds bits [4q, 4q+4): word q>>3, nibble q&7
         float4* d = dst + lg;
         const int iters = (nf4 - lg + G - 1) / G;
@@ -716,6 +731,15 @@ dec_env_kernel(const DecParams p) {
     constexpr int G = SP::G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ float4 lut[16];
+#if MCOV_LUT8
+    __shared__ float4 lut8[512];
+    for (int t = threadIdx.x; t < 512; t += blockDim.x) {
+        const uint32_t n = ((uint32_t)t >> 1), h = (n >> (4 * (t & 1))) & 15u;
+        lut8[t] = make_float4((h & 1u) ? 1.0f : 0.0f, (h & 2u) ? 1.0f : 0.0f, (h & 4u) ? 1.0f : 0.0f, (h & 8u) ? 1.0f : 0.0f);
+    }
+#else
+    const float4* lut8 = nullptr;
+#endif
     __shared__ int last_flag;
     const Grp<G> g(threadIdx.x & 31);
     // Spec::ST: st_warps of the CTA's warps are store warps, the others are pass warps.  The store warps of the
@@ -796,7 +820,7 @@ dec_env_kernel(const DecParams p) {
         } else if (act) {
             const int e_next = (mode == MODE_STEP && e + gtot < p.E) ? e + gtot : -1;
             int r;
-            while ((r = env_pass<SP>(p, sm, lut, e, m, cur, g, nxt, e_next, link)) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
+            while ((r = env_pass<SP>(p, sm, lut, lut8, e, m, cur, g, nxt, e_next, link)) == PASS_AGAIN) m = MODE_RESET;   // fused auto-reset
             has_block = (r == PASS_STORE);
             ++link.it;
         }
@@ -1056,6 +1080,7 @@ inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
         // for lidar windows: 2 x 83 kB CTAs hold 64 groups where 5 x 41 kB CTAs hold 80)
         int best = 0;
         for (int warps = MAX_WARPS; warps >= 1; warps >>= 1) {
+            if (env->pin_warps >= 1 && warps != env->pin_warps && env->pin_warps <= MAX_WARPS) continue;   // MCOV_DEC_WARPS pins the CTA size
             const int gr = warps * per_warp;
             size_t sm_bytes = s.grp_smem * gr;
             if (sm_bytes < (size_t)warps * 32 * 8) sm_bytes = (size_t)warps * 32 * 8;

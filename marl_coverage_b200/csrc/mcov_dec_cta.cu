@@ -23,6 +23,10 @@
 #include "mcov_internal.h"
 #include "mcov_dec_shared.cuh"
 
+#ifndef MCOV_LIDAR_RUNTAB
+#define MCOV_LIDAR_RUNTAB 0                  // see mcov_dec.cu
+#endif
+
 namespace mcov {
 
 namespace {
@@ -331,6 +335,9 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
         if (p.lidar_cells) {
             if (!((ww[R] >> R) & 1u)) {
                 for (int l = lane; l < p.n_lasers; l += 32) {
+#if MCOV_LIDAR_RUNTAB
+                    walk_beam_runs(p.lidar_runs, l, ww, wf, wo);
+#else
                     const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
                     const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
                     const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
@@ -342,6 +349,7 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
                         if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
                         atomicOr(&wf[rx], 1u << ry);
                     }
+#endif
                 }
             }
         } else {

@@ -61,6 +61,32 @@ __device__ __forceinline__ uint32_t ymask_in_strip(int yj, int R, int S, int s) 
 }
 
 
+// Integer beam table walk (lidar.py:30-65 restated on the proved start-independent cell list, mcov_set_lidar_beams): the
+// cells of beam l after the robot's own one, as same-row runs.  `ww` / `wf` / `wo` are the robot's truth-wall, free-hit and
+// obstacle-hit windows in shared memory (one word per window row).  Per run: no wall in it -> all its cells are free hits;
+// otherwise the first wall in march order is the obstacle hit, the cells before it are free hits, and the beam ends.
+__device__ __forceinline__ void walk_beam_runs(const uint2* __restrict__ runs, int l, const uint32_t* ww, uint32_t* wf,
+                                               uint32_t* wo) {
+    const uint2* tb = runs + l * 16;
+    uint2 r = __ldg(tb);
+#pragma unroll 1
+    for (int k = 1; r.x != 0u; ++k) {
+        const uint2 nx = k < 16 ? __ldg(tb + k) : make_uint2(0u, 0u);        // next run, in flight behind this one
+        const uint32_t row = (r.y & 0x7fffffffu) >> 2;
+        const uint32_t hit = ww[row] & r.x;
+        if (hit) {
+            uint32_t first, freeb;
+            if (r.y >> 31) { first = 0x80000000u >> __clz(hit); freeb = r.x & ~((first << 1) - 1u); }
+            else { first = hit & (0u - hit); freeb = r.x & (first - 1u); }
+            if (freeb) atomicOr(wf + row, freeb);
+            atomicOr(wo + row, first);
+            break;
+        }
+        atomicOr(wf + row, r.x);
+        r = nx;
+    }
+}
+
 // ---- episode statistics: per-group (or per-CTA) sums in shared memory -> one row per CTA in global scratch ->
 // the last-arriving CTA folds all rows into stats_out (single launch, graph-capturable).  `rows` holds `nrows`
 // records of MCOV_STATS_LEN doubles, `row_stride` bytes apart; `red` is blockDim.x doubles of shared memory that

@@ -22,6 +22,8 @@ struct DecParams {
     int n_lasers;
     const double* beams;      // [n_lasers][3] device
     const uint16_t* lidar_cells;  // [n_lasers][16] window cells of each beam in march order (0xffff ends), or null
+    const uint2* lidar_runs;      // [n_lasers][16] the same cells grouped into same-row runs: {bit mask of the run's cells,
+                                  // row byte offset | bit 31 = cells are marched towards lower y}, mask 0 ends the beam
     uint32_t l_magic;         // ceil(2^32 / n_lasers)
     uint32_t l_mult;          // beam permutation of the table walk: l -> l * l_mult mod n_lasers (coprime)
     int single_tool, comm_radius, want_adj, dist_reward;
@@ -168,6 +170,7 @@ struct mcov_env {
     unsigned char* arena;
     double* beams_dev;        // owned
     uint16_t* lidar_cells_dev; // owned; null when the integer beam table could not be proven exact
+    uint2* lidar_runs_dev;     // owned; same table as same-row runs (null with lidar_cells_dev)
     int64_t launches;
     uint64_t seed;            // seed of the last mcov_reset (auto-reset draws derive from it)
     int obs_C;
@@ -175,7 +178,7 @@ struct mcov_env {
     // tuning / test pins read from the environment once, at mcov_create (-1 = not pinned):
     // MCOV_DEC_GROUP (lanes per env), MCOV_DEC_STORE (store-warp path 0|1), MCOV_DEC_GRID (grid cap),
     // MCOV_DEC_NBUF (staging buffers per store warp), MCOV_DEC_SW (store warps per CTA), MCOV_DEC_SHAPE (0 lane groups, 1 CTA per env), MCOV_DEC_TMA (CTA shape: 0 plain loads, 1 bulk-copy staging)
-    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma, pin_team;
+    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma, pin_team, pin_warps;
     size_t dec_smem_configured, super_smem_configured;   // dynamic shared memory opted into on this handle's device
     const void* dec_smem_func;  // ... and for which instantiation (MCOV_DEC_GROUP can change it between launches)
     const double* cell_values;  // Super: float64 [n_maps][W][L] reward of covering a cell, or null (= 1.0)
