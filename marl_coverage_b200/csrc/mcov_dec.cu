@@ -117,7 +117,7 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
 #define MCOV_PRAGMA_(x) _Pragma(#x)
 #define MCOV_UNROLL(n) MCOV_PRAGMA_(unroll n)
 #ifndef MCOV_LUT8
-#define MCOV_LUT8 0                          // observation store: byte -> 2 x float4 table (8 kB of shared memory per CTA)
+#define MCOV_LUT8 0                          // observation store: byte -> 2 x float4 table (8 kB of shared memory per CTA): 1 = two 128-bit stores, 2 = one 256-bit store
 #endif
 #ifndef MCOV_NO_PF
 #define MCOV_NO_PF 0                         // 1: drop the L1 prefetch of the window runs before the band-row loop
@@ -689,8 +689,9 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     if (p.vec_ok) {
         float4* dst = reinterpret_cast<float4*>(obs_e);
         const int nf4 = p.obs_env_floats >> 2;
-#if MCOV_LUT8
-        // one byte of the bit stream -> two float4 through a 256-entry table: 4 instead of 7 instructions per float4
+#if MCOV_LUT8 == 1
+        // one byte of the bit stream -> two float4 through a 256-entry table, two 128-bit stores per lane
+        // (A/B on C5: 0.243 vs 0.196 ms — a lane's stores are 32 bytes apart, every instruction half-fills its sectors)
         {
             const int np = nf4 >> 1;
             float4* d2 = dst + 2 * lg;
@@ -706,6 +707,33 @@ MCOV_UNROLL(MCOV_ST_UNROLL)
             if ((nf4 & 1) && lg == 0) {
                 const int q = nf4 - 1;
                 obs_store(dst + q, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
+            }
+            return PASS_DONE;
+        }
+#elif MCOV_LUT8 == 2
+        // ... and one 256-bit store per lane (st.global.v8.f32, sm_100): a block that starts 16 bytes off a 32-byte
+        // boundary (every other env at C2: 5808-byte blocks) peels its first float4, the byte is then cut from the
+        // bit stream at a 4-bit phase
+        {
+            const int h = (int)((reinterpret_cast<uintptr_t>(dst) >> 4) & 1u);
+            const int np = (nf4 - h) >> 1;
+            if (lg == 0) {
+                if (h) obs_store(dst, lut[sm.bits[0] & 15u]);
+                if ((nf4 - h) & 1) {
+                    const int q = nf4 - 1;
+                    obs_store(dst + q, lut[(sm.bits[q >> 3] >> ((q & 7) * 4)) & 15u]);
+                }
+            }
+            float4* d2 = dst + h + 2 * lg;
+            const int it2 = (np - lg + G - 1) / G;
+MCOV_UNROLL(MCOV_ST_UNROLL)
+            for (int t = 0; t < it2; ++t) {
+                const int pos = 4 * h + 8 * (lg + t * G);
+                const uint32_t byte = __funnelshift_r(sm.bits[pos >> 5], sm.bits[(pos >> 5) + 1], pos & 31) & 255u;
+                const float4 v0 = lut8[2 * byte], v1 = lut8[2 * byte + 1];
+                asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                             :: "l"(d2 + 2 * t * G), "f"(v0.x), "f"(v0.y), "f"(v0.z), "f"(v0.w), "f"(v1.x), "f"(v1.y), "f"(v1.z), "f"(v1.w)
+                             : "memory");
             }
             return PASS_DONE;
         }
