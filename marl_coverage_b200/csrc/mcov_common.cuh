@@ -51,18 +51,6 @@ __device__ __forceinline__ uint32_t read_window(const uint32_t* __restrict__ pla
     return __funnelshift_r(lo, hi, sh) & low_mask(width);
 }
 
-// Same for the interleaved per-robot {free, obst} planes (not read-only: plain loads).
-__device__ __forceinline__ uint2 read_window2(const uint2* plane, int Wp, int strips, int x,
-                                              int y0, int width) {
-    const int s0 = y0 >> 5;
-    const int sh = y0 & 31;
-    uint2 lo = make_uint2(0, 0), hi = make_uint2(0, 0);
-    if (s0 >= 0 && s0 < strips) lo = plane[s0 * Wp + x];
-    if (sh + width > 32 && s0 + 1 >= 0 && s0 + 1 < strips) hi = plane[(s0 + 1) * Wp + x];
-    const uint32_t m = low_mask(width);
-    return make_uint2(__funnelshift_r(lo.x, hi.x, sh) & m, __funnelshift_r(lo.y, hi.y, sh) & m);
-}
-
 __device__ __forceinline__ int get_bit(const uint32_t* __restrict__ plane, int Wp, int x, int y) {
     return (__ldg(plane + (y >> 5) * Wp + x) >> (y & 31)) & 1u;
 }
@@ -73,13 +61,6 @@ __device__ __forceinline__ void split_words(uint32_t rel, int y0, uint32_t& lo, 
     const uint64_t v = (uint64_t)rel << sh;
     lo = (uint32_t)v;
     hi = (uint32_t)(v >> 32);
-}
-
-// Move a row of window bits from one window frame to another (delta = new_origin_offset).
-// out bit b = in bit (b - delta): delta >= 0 shifts left.
-__device__ __forceinline__ uint32_t shift_bits(uint32_t v, int delta) {
-    if (delta >= 32 || delta <= -32) return 0;
-    return delta >= 0 ? (v << delta) : (v >> (-delta));
 }
 
 // ---- Philox4x32-10 (device RNG for reset draws; keyed by seed, counter = env/episode/draw) ------
@@ -167,14 +148,13 @@ __device__ __forceinline__ void bulk_store_s2g(void* gdst, const void* ssrc, uin
                  :: "l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
-__device__ __forceinline__ void bulk_wait_read_all() {
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-}
 __device__ __forceinline__ void bulk_wait_all() {
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
-// ---- async bulk load global -> shared with mbarrier completion (map-window staging) -------------
+// ---- async bulk load global -> shared with mbarrier completion (map-window staging, mcov_dec_cta.cu) ----
+// The destination is named in the shared::cluster window: without a cluster launch a CTA's own shared::cta
+// addresses are valid shared::cluster addresses of itself (PTX ISA, "shared memory state space").
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
 }

@@ -119,6 +119,9 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
 #ifndef MCOV_LUT8
 #define MCOV_LUT8 0                          // observation store: byte -> 2 x float4 table (8 kB of shared memory per CTA): 1 = two 128-bit stores, 2 = one 256-bit store
 #endif
+#ifndef MCOV_PF_EARLY
+#define MCOV_PF_EARLY 0                      // 1: prefetch the window runs for the pre-move band (grown by one cell) before the moves
+#endif
 #ifndef MCOV_NO_PF
 #define MCOV_NO_PF 0                         // 1: drop the L1 prefetch of the window runs before the band-row loop
 #endif
@@ -284,6 +287,37 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     int cov_old = 0;
     if (mode == MODE_STEP && lg < N) cov_old = hcov[lg];
 
+#if MCOV_PF_EARLY
+    if (!fresh && mode == MODE_STEP) {
+        // The band can only move by one cell: pull the lines under the PRE-move band, grown by one row either side and
+        // one cell up and down, towards the SM before the wall bits are fetched and the moves resolved — the loads of
+        // the band-row loop are then a move's worth of instructions behind their prefetch instead of a few dozen.
+        for (int base = 0; base < 2 * N; base += G) {             // every lane of the group takes part in the shuffle
+            const int idx = base + lg, i = idx >> 1, k = idx & 1;
+            const uint32_t pi = (uint32_t)g.shfl((int)myv, i & (G - 1));
+            if (idx >= 2 * N) continue;
+            const int xi = unpack_x(pi), yi = unpack_y(pi);
+            const int yb = yi - rad - 1;
+            const int s = (yb >> 5) + k;
+            if (s < 0 || s >= strips || (k == 1 && (yb & 31) + RW + 2 <= 32)) continue;
+            const int xa = max(xi - rad - 1, 0), xb = min(xi + rad + 1, W - 1);
+            const uint32_t fw = (eN + i) * PW + s * Wp;
+            prefetch_l1(fo_g + fw + xa);
+            prefetch_l1(fo_g + fw + xb);
+            if (s >= ((yi - R - 1) >> 5) && s <= ((yi + R + 1) >> 5)) {
+                const int xc = max(xi - R - 1, 0), xd = min(xi + R + 1, W - 1);
+                prefetch_l1(vis_g + vis_off + s * Wp + xc);
+                prefetch_l1(vis_g + vis_off + s * Wp + xd);
+                prefetch_l1(wall_g + map_off + s * Wp + xc);
+                prefetch_l1(wall_g + map_off + s * Wp + xd);
+                if (!LIDAR) {
+                    prefetch_l1(tpos_g + map_off + s * Wp + xc);
+                    prefetch_l1(tpos_g + map_off + s * Wp + xd);
+                }
+            }
+        }
+    }
+#endif
     int px = unpack_x(myv), py = unpack_y(myv);
     int ncoll = 0;
     bool sentinel = false;
@@ -355,7 +389,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     g.sync();
 
     const bool do_sense = fresh || (mode == MODE_STEP && !sentinel);
-    if (!fresh && !MCOV_NO_PF) {
+    if (!fresh && !MCOV_NO_PF && !(MCOV_PF_EARLY && mode == MODE_STEP)) {
         // Pull the lines under every robot's window towards the SM now: band rows are contiguous in
         // x within a strip ((2*rad+1) * 8 B <= 2 lines), so touching the first and last row of each
         // run covers it.  One lane per (robot, strip); the slot loop below then hits L1/L2 instead
