@@ -388,6 +388,14 @@ int mcov_set_lidar_beams(mcov_env* env, const double* beams_host, int num_lasers
         for (int j = nr; ok && j < 16; ++j) runs[(size_t)l * 16 + j] = make_uint2(0u, 0u);
     }
     if (ok) {
+        // device format of a cell: low byte = y bit of the cell in its window row, high byte = byte offset of the row
+        // word (4 * row); the slots behind a beam's last cell point at row S, a dummy row the kernels keep all-wall, so
+        // the walk needs no end-of-list test: it stops there like at any obstacle
+        const int S = 2 * R + 1;
+        for (size_t k = 0; k < (size_t)num_lasers * 16; ++k) {
+            const uint16_t c = table[k];
+            table[k] = c == 0xffffu ? (uint16_t)((4 * S) << 8) : (uint16_t)((c >> 8) | ((4 * (c & 0xff)) << 8));
+        }
         ce = cudaMalloc(&env->lidar_cells_dev, sizeof(uint16_t) * 16 * num_lasers);
         if (ce == cudaSuccess)
             ce = cudaMemcpy(env->lidar_cells_dev, table, sizeof(uint16_t) * 16 * num_lasers, cudaMemcpyHostToDevice);

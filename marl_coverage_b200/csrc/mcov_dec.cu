@@ -106,8 +106,8 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
     s.nearM = s.posF + p.N;
     s.covS = reinterpret_cast<int*>(s.nearM + p.N);
     s.winF = reinterpret_cast<uint32_t*>(s.covS + p.N);
-    s.winO = s.winF + p.N * p.S;
-    s.wallW = s.winO + p.N * p.S;
+    s.winO = s.winF + p.N * (p.S + 1);                 // S window rows + the dummy row of the beam table walk
+    s.wallW = s.winO + p.N * (p.S + 1);
     return s;
 }
 
@@ -227,7 +227,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
     const bool single_tool = !SP::FIXED && p.single_tool;
     const int comm_radius = SP::FIXED ? 0 : p.comm_radius;
     const int phases = SP::FIXED ? (PH_MOVE | PH_SENSE) : p.phases;          // split only for dist_reward (C == 4)
-    const int S = 2 * R + 1, ow = 2 * ego + 1, rad = ego > R ? ego : R, RW = 2 * rad + 1;
+    const int S = 2 * R + 1, Sp = S + 1, ow = 2 * ego + 1, rad = ego > R ? ego : R, RW = 2 * rad + 1;
     const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
     const int lg = g.lg;
     auto div_n = [&](int k) { return SP::FIXED ? k / (SP::FIXED ? SP::CN : 1) : fast_div(k, p.n_magic); };
@@ -434,14 +434,15 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 const uint32_t pi = sm.posF[i];
                 const int x = unpack_x(pi) - R + r, y0 = unpack_y(pi) - R;
                 const uint32_t wrow = (x >= 0 && x < W) ? read_window(wall_g + map_off, Wp, strips, x, y0, S) : 0xffffffffu;
-                sm.wallW[idx] = wrow;
+                sm.wallW[i * Sp + r] = wrow;
                 // table walk: every beam starts on the robot's own cell, lidar.py:30 — set it here once instead of
                 // by n_lasers colliding shared-memory atomics.  (A robot never stands on an obstacle inside the env;
                 // a sensor probe can put one there: then every beam ends at once on that cell, lidar.py:58-63.)
                 const bool own_wall = (wrow >> R) & 1u;
-                sm.winF[idx] = (p.lidar_cells && r == R && !own_wall) ? (1u << R) : 0u;
-                sm.winO[idx] = (p.lidar_cells && r == R && own_wall) ? (1u << R) : 0u;
+                sm.winF[i * Sp + r] = (p.lidar_cells && r == R && !own_wall) ? (1u << R) : 0u;
+                sm.winO[i * Sp + r] = (p.lidar_cells && r == R && own_wall) ? (1u << R) : 0u;
             }
+            if (lg < N) sm.wallW[lg * Sp + S] = 0xffffffffu;        // dummy row of the beam table walk: all wall
             g.sync();
             if (p.lidar_cells) {
                 // integer beam table (proved start-independent on the host, mcov_set_lidar_beams):
@@ -459,24 +460,14 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
 #else
                     const int l = l0;
 #endif
-                    const uint32_t* ww = sm.wallW + i * S;
-                    uint32_t* wf = sm.winF + i * S;
-                    uint32_t* wo = sm.winO + i * S;
+                    const uint32_t* ww = sm.wallW + i * Sp;
+                    uint32_t* wf = sm.winF + i * Sp;
+                    uint32_t* wo = sm.winO + i * Sp;
                     if ((ww[R] >> R) & 1u) continue;               // own cell is an obstacle: the beam ended there
 #if MCOV_LIDAR_RUNTAB
                     walk_beam_runs(p.lidar_runs, l, ww, wf, wo);
 #else
-                    const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
-                    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
-                    const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
-#pragma unroll
-                    for (int k = 1; k < 16; ++k) {
-                        const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
-                        if (cell == 0xffffu) break;
-                        const int rx = (int)(cell & 0xffu), ry = (int)(cell >> 8);
-                        if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
-                        atomicOr(&wf[rx], 1u << ry);
-                    }
+                    walk_beam_cells(p.lidar_cells, l, ww, wf, wo);
 #endif
                 }
             } else {
@@ -495,16 +486,16 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     rx = __double2int_rz(cx) - (xi - R);
                     ry = __double2int_rz(cy) - (yi - R);
                     const bool inwin = rx >= 0 && rx < S && ry >= 0 && ry < S;
-                    walk = inside && inwin && !((sm.wallW[i * S + rx] >> ry) & 1u);
+                    walk = inside && inwin && !((sm.wallW[i * Sp + rx] >> ry) & 1u);
                     if (!(walk && dist < rng)) break;
-                    atomicOr(&sm.winF[i * S + rx], 1u << ry);
+                    atomicOr(&sm.winF[i * Sp + rx], 1u << ry);
                     cx += xinc;
                     cy += yinc;
                     dist += dinc;
                 }
                 if (rx >= 0 && rx < S && ry >= 0 && ry < S) {
-                    if (walk) atomicOr(&sm.winF[i * S + rx], 1u << ry);
-                    else atomicOr(&sm.winO[i * S + rx], 1u << ry);
+                    if (walk) atomicOr(&sm.winF[i * Sp + rx], 1u << ry);
+                    else atomicOr(&sm.winO[i * Sp + rx], 1u << ry);
                 }
             }
             }
@@ -512,7 +503,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 g.sync();
                 for (int idx = lg; idx < N * S; idx += G) {
                     const int i = div_s(idx), r = idx - i * S;
-                    sm.winF[idx] = (r == R) ? (1u << R) : 0u;      // dec_grid_rl.py:233-234
+                    sm.winF[i * Sp + r] = (r == R) ? (1u << R) : 0u;      // dec_grid_rl.py:233-234
                 }
             }
         }
@@ -566,8 +557,8 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             }
         } else if (sens) {
             const int r = a2 - rad + R;
-            split_words(sm.winF[i * S + r] << (rad - R), y0r, f0, f1);
-            split_words(sm.winO[i * S + r] << (rad - R), y0r, o0, o1);
+            split_words(sm.winF[i * Sp + r] << (rad - R), y0r, f0, f1);
+            split_words(sm.winO[i * Sp + r] << (rad - R), y0r, o0, o1);
             if (!in0) { f0 = 0; o0 = 0; }
             if (!in1) { f1 = 0; o1 = 0; }
         }
@@ -596,7 +587,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     uint32_t add;
                     if (LIDAR) {
                         uint32_t jl, jh;
-                        split_words(sm.winF[j * S + (x - xj + R)], y0j, jl, jh);
+                        split_words(sm.winF[j * Sp + (x - xj + R)], y0j, jl, jh);
                         add = (sk == s0j) ? jl : jh;
                     } else if (single_tool) {
                         add = (x == xj && (yj >> 5) == sk) ? (1u << (yj & 31)) : 0u;
@@ -1109,7 +1100,7 @@ inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
     s.bits_words = (N * env->obs_C * ow * ow + 31) / 32 + 1;
     s.slot_words = s.st ? round_up(s.bits_words + 1, 2) : 0;       // + the env id word
     s.nbuf = 0; s.bar_off = 0; s.stage_off = 0; s.stage_pitch = 0; s.nsw = 1;
-    int words = (s.st ? 2 * s.slot_words : s.bits_words) + 3 * N + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 * N * S : 0);
+    int words = (s.st ? 2 * s.slot_words : s.bits_words) + 3 * N + (c.sensor_type == MCOV_SENSOR_LIDAR ? 3 * N * (S + 1) : 0);
     words = round_up(words, 2);
     // stagger the groups of one warp over the 32 banks: stride = multiple of 32 words + G
     int stride_words = MCOV_STATS_LEN * 2 + words;

@@ -57,7 +57,7 @@ __host__ __device__ inline size_t cta_carve(unsigned char* base, int N, int S, i
     const size_t o_stats = take(MCOV_STATS_LEN * 8, 16), o_bits = take((size_t)bits_words * 4, 16);
     const size_t o_pos = take((size_t)N * 4, 4), o_posf = take((size_t)N * 4, 4), o_cnt = take((size_t)N * 4, 4), o_cov = take((size_t)N * 4, 4);
     const size_t o_flags = take(16, 16);
-    const size_t nwin = lidar ? (size_t)N * S * 4 : 0;
+    const size_t nwin = lidar ? (size_t)N * (S + 1) * 4 : 0;        // S window rows + the dummy row of the beam table walk
     const size_t o_wf = take(nwin, 4), o_wo = take(nwin, 4), o_ww = take(nwin, 4);
     const size_t o_bars = take((size_t)N * 8, 8), o_stage = take((size_t)N * STAGE_BYTES, 128);
     if (s) {
@@ -115,7 +115,7 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
     const int N = p.N, R = p.R, ego = p.ego, C = p.C;
     const bool single_tool = p.single_tool != 0;
     const int comm_radius = p.comm_radius, phases = p.phases;
-    const int S = 2 * R + 1, ow = 2 * ego + 1, rad = p.rad, RW = p.RW;
+    const int S = 2 * R + 1, Sp = S + 1, ow = 2 * ego + 1, rad = p.rad, RW = p.RW;
     const int W = p.g.W, L = p.g.L, Wp = p.g.Wp, strips = p.g.strips, PW = p.g.PW;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;       // warp w <-> robot w
 
@@ -320,9 +320,10 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
     }
     if (LIDAR && do_sense) {
         // lidar.py:16-65 — stage the truth wall window of robot i, then march its beams (lanes = beams)
-        uint32_t* ww = sm.wallW + i * S;
-        uint32_t* wf = sm.winF + i * S;
-        uint32_t* wo = sm.winO + i * S;
+        uint32_t* ww = sm.wallW + i * Sp;
+        uint32_t* wf = sm.winF + i * Sp;
+        uint32_t* wo = sm.winO + i * Sp;
+        if (lane == 0) ww[S] = 0xffffffffu;                          // dummy row: all wall
         if (lane < S) {
             const int x = xi - R + lane, y0 = yi - R;
             const uint32_t wrow = (x >= 0 && x < W) ? read_window(wall_g + map_off, Wp, strips, x, y0, S) : 0xffffffffu;
@@ -338,17 +339,7 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
 #if MCOV_LIDAR_RUNTAB
                     walk_beam_runs(p.lidar_runs, l, ww, wf, wo);
 #else
-                    const uint4* tp = reinterpret_cast<const uint4*>(p.lidar_cells + l * 16);
-                    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
-                    const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
-#pragma unroll
-                    for (int k = 1; k < 16; ++k) {
-                        const uint32_t cell = (c[k >> 1] >> (16 * (k & 1))) & 0xffffu;
-                        if (cell == 0xffffu) break;
-                        const int rx = (int)(cell & 0xffu), ry = (int)(cell >> 8);
-                        if ((ww[rx] >> ry) & 1u) { atomicOr(&wo[rx], 1u << ry); break; }
-                        atomicOr(&wf[rx], 1u << ry);
-                    }
+                    walk_beam_cells(p.lidar_cells, l, ww, wf, wo);
 #endif
                 }
             }
@@ -456,8 +447,8 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
             }
         } else if (sens) {
             const int r = a2 - rad + R;
-            split_words(sm.winF[i * S + r] << (rad - R), y0r, f0, f1);
-            split_words(sm.winO[i * S + r] << (rad - R), y0r, o0, o1);
+            split_words(sm.winF[i * Sp + r] << (rad - R), y0r, f0, f1);
+            split_words(sm.winO[i * Sp + r] << (rad - R), y0r, o0, o1);
             if (!in0) { f0 = 0; o0 = 0; }
             if (!in1) { f1 = 0; o1 = 0; }
         }
@@ -484,7 +475,7 @@ __device__ __forceinline__ int cta_pass(const DecParams& p, const CtaSmem& sm, c
                     uint32_t add;
                     if (LIDAR) {
                         uint32_t jl, jh;
-                        split_words(sm.winF[j * S + (x - xj + R)], y0j, jl, jh);
+                        split_words(sm.winF[j * Sp + (x - xj + R)], y0j, jl, jh);
                         add = (sk == s0j) ? jl : jh;
                     } else if (single_tool) {
                         add = (x == xj && (yj >> 5) == sk) ? (1u << (yj & 31)) : 0u;

@@ -61,6 +61,27 @@ __device__ __forceinline__ uint32_t ymask_in_strip(int yj, int R, int S, int s) 
 }
 
 
+// Integer beam table walk, cell by cell (lidar.py:30-65 on the proved start-independent cell list, mcov_set_lidar_beams).
+// `ww` / `wf` / `wo`: the robot's truth-wall, free-hit and obstacle-hit windows in shared memory, S + 1 words each — row S
+// is a dummy the caller keeps all-wall (ww) / uses as a sink (wo), so a beam's unused slots end the walk like an obstacle.
+__device__ __forceinline__ void walk_beam_cells(const uint16_t* __restrict__ cells, int l, const uint32_t* ww, uint32_t* wf,
+                                                uint32_t* wo) {
+    const uint4* tp = reinterpret_cast<const uint4*>(cells + l * 16);
+    const uint4 ta = __ldg(tp), tb = __ldg(tp + 1);
+    const uint32_t c[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
+    const unsigned char* wwb = reinterpret_cast<const unsigned char*>(ww);
+    unsigned char* wfb = reinterpret_cast<unsigned char*>(wf);
+    unsigned char* wob = reinterpret_cast<unsigned char*>(wo);
+#pragma unroll
+    for (int k = 1; k < 16; ++k) {
+        const uint32_t cell = (k & 1) ? (c[k >> 1] >> 16) : (c[k >> 1] & 0xffffu);
+        const uint32_t off = cell >> 8;                              // byte offset of the row word
+        const uint32_t m = __funnelshift_l(0u, 1u, cell);            // 1 << (cell & 31): the y bit
+        if (*reinterpret_cast<const uint32_t*>(wwb + off) & m) { atomicOr(reinterpret_cast<uint32_t*>(wob + off), m); break; }
+        atomicOr(reinterpret_cast<uint32_t*>(wfb + off), m);
+    }
+}
+
 // Integer beam table walk (lidar.py:30-65 restated on the proved start-independent cell list, mcov_set_lidar_beams): the
 // cells of beam l after the robot's own one, as same-row runs.  `ww` / `wf` / `wo` are the robot's truth-wall, free-hit and
 // obstacle-hit windows in shared memory (one word per window row).  Per run: no wall in it -> all its cells are free hits;

@@ -21,7 +21,8 @@ struct DecParams {
     int sensor;               // MCOV_SENSOR_*
     int n_lasers;
     const double* beams;      // [n_lasers][3] device
-    const uint16_t* lidar_cells;  // [n_lasers][16] window cells of each beam in march order (0xffff ends), or null
+    const uint16_t* lidar_cells;  // [n_lasers][16] window cells of each beam in march order: y bit | (4 * row) << 8; slots behind
+                                  // the last cell name the dummy all-wall row S; slot 0 (the robot's own cell) is not walked; or null
     const uint2* lidar_runs;      // [n_lasers][16] the same cells grouped into same-row runs: {bit mask of the run's cells,
                                   // row byte offset | bit 31 = cells are marched towards lower y}, mask 0 ends the beam
     uint32_t l_magic;         // ceil(2^32 / n_lasers)
