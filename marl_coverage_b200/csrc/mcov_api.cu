@@ -304,6 +304,7 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
     e->pin_tma = pin("MCOV_DEC_TMA");
     e->pin_team = pin("MCOV_DEC_TEAM");
     e->pin_warps = pin("MCOV_DEC_WARPS");
+    e->pin_balance = pin("MCOV_DEC_BALANCE");
     *out = e;
     return MCOV_OK;
 }

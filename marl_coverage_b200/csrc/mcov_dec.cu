@@ -1144,6 +1144,24 @@ inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
             if (ps > 16) ps = 16;
             if (ps * gr > best) { best = ps * gr; groups = gr; per_sm = ps; }
         }
+        // One wave (every env has a lane group resident at once): what counts is the busiest SM, so size the CTAs to
+        // spread the batch's warps evenly — 4096 envs at 32 lanes are 4096 warps = 27.7 per SM: 512 CTAs of 8 warps put
+        // 32 warps on some SMs and 24 on others, 586 CTAs of 7 warps put 28 on (almost) every one.
+        if (env->pin_warps < 1 && env->pin_balance != 0) {
+            const long long total_warps = ((long long)c.num_envs + per_warp - 1) / per_warp;
+            const int cap_warps = per_sm * (groups / per_warp);           // resident warps per SM of the choice above
+            const int wps = (int)((total_warps + env->num_sms - 1) / env->num_sms);
+            if (wps <= cap_warps) {
+                int best_w = groups / per_warp, best_waste = 1 << 30;
+                for (int w = MAX_WARPS; w >= 1; --w) {
+                    if (((w * 32) & 7) != 0) continue;
+                    const int waste = (wps + w - 1) / w * w - wps;
+                    if (waste < best_waste) { best_waste = waste; best_w = w; }
+                }
+                groups = best_w * per_warp;
+                per_sm = (wps + best_w - 1) / best_w;
+            }
+        }
         s.threads = groups * s.G;
         s.smem = s.grp_smem * groups;
     }

@@ -130,7 +130,8 @@ __device__ __forceinline__ void fold_episode_stats(const DecParams& p, const uns
         __threadfence();
         const int k = threadIdx.x & (MCOV_STATS_LEN - 1), r0 = threadIdx.x >> 3, rstep = blockDim.x >> 3;
         double s = 0.0;
-        for (int r = r0; r < (int)gridDim.x; r += rstep)
+#pragma unroll 8
+        for (int r = r0; r < (int)gridDim.x; r += rstep)           // loads of 8 rows in flight, summed in row order
             s += __ldcg(p.stats_partial + (size_t)r * MCOV_STATS_LEN + k);
         __syncthreads();
         red[threadIdx.x] = s;
