@@ -11,6 +11,7 @@ from .vec_env import VecDecGridRL, VecSuperGridRL               # noqa: F401
 from .envs import DecGridRL, SuperGridRL                        # noqa: F401
 from .replay import ReplayBuffer, collect                       # noqa: F401
 from .sim_env import SuperGrid_Sim, VecSuperGridSim             # noqa: F401
+from .rollout import RolloutGraph                               # noqa: F401
 
 __all__ = ["DecGridRL", "SuperGridRL", "VecDecGridRL", "VecSuperGridRL", "Sensor", "SquareSensor",
-           "LidarSensor", "Discrete", "ReplayBuffer", "collect", "SuperGrid_Sim", "VecSuperGridSim", "Base_Space", "gridload", "gridgen", "load_grid_set", "MapTable"]
+           "LidarSensor", "Discrete", "ReplayBuffer", "collect", "SuperGrid_Sim", "VecSuperGridSim", "Base_Space", "gridload", "gridgen", "load_grid_set", "MapTable", "RolloutGraph"]

@@ -167,3 +167,40 @@ def test_caller_buffers_are_validated():
     twin.reset(seed=3)
     twin.step(act)
     assert torch.equal(twin.step(act)[0], env.step(act)[0])
+
+
+@pytest.mark.parametrize("kind,keep_obs", [("dec", False), ("dec", True), ("super", False)])
+def test_rollout_graph_helper_equals_eager(kind, keep_obs):
+    """marl_coverage_b200.RolloutGraph: K steps captured once, replayed with new actions each time, against the same
+    steps taken one by one — rewards, done flags, statistics, observations, state; fused auto-resets included."""
+    import torch
+    from marl_coverage_b200 import RolloutGraph, VecDecGridRL, VecSuperGridRL, load_grid_set
+    grids = load_grid_set("bg2_100x100", 5)
+    cfg = dict(SUPER) if kind == "super" else dict(DEC)
+    cls = VecSuperGridRL if kind == "super" else VecDecGridRL
+    E, N, K, rounds = 97, cfg["numrobot"], 8, 5
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(11)
+    acts = torch.randint(0, 4, (rounds, K, E, N), dtype=torch.uint8, device="cuda", generator=gen)
+    envs = []
+    for _ in range(2):
+        env = cls(grids, cfg, num_envs=E, auto_reset=True, truncate_steps=30, seed=9)
+        env.reset(seed=77)
+        envs.append(env)
+    eager, graphed = envs
+    roll = RolloutGraph(graphed, K, keep_obs=keep_obs)
+    ns = graphed.layout.off_scratch                                 # state proper; behind it: library scratch
+    assert torch.equal(graphed.obs, eager.obs) and torch.equal(graphed._arena[:ns], eager._arena[:ns])   # capture left no trace
+    episodes = 0.0
+    for r in range(rounds):
+        rew, done = roll.replay(acts[r])
+        for k in range(K):
+            o, _, d = eager.step(acts[r, k], want_stats=True)
+            assert torch.equal(roll.reward64[k], eager.reward64) and torch.equal(done[k], d), "round %d step %d" % (r, k)
+            assert torch.equal(roll.stats[k], eager.stats)
+            if keep_obs:
+                assert torch.equal(roll.obs_log[k], o)
+            episodes += float(eager.stats[0].item())
+        assert torch.equal(graphed.obs, eager.obs)
+        assert torch.equal(graphed._arena[:graphed.layout.off_scratch], eager._arena[:eager.layout.off_scratch])
+    assert episodes > 0
