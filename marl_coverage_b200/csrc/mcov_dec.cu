@@ -119,6 +119,9 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
 #ifndef MCOV_LUT8
 #define MCOV_LUT8 0                          // observation store: byte -> 2 x float4 table (8 kB of shared memory per CTA): 1 = two 128-bit stores, 2 = one 256-bit store
 #endif
+#ifndef MCOV_PF_TRIM
+#define MCOV_PF_TRIM 0                       // L1 prefetch before the band-row loop: 0 first+last row of every run, 1 one per 1-bit run, 2 own planes only
+#endif
 #ifndef MCOV_PF_EARLY
 #define MCOV_PF_EARLY 0                      // 1: prefetch the window runs for the pre-move band (grown by one cell) before the moves
 #endif
@@ -404,6 +407,18 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             const uint32_t fw = (eN + i) * PW + s * Wp;
             prefetch_l1(fo_g + fw + xa);
             prefetch_l1(fo_g + fw + xb);
+#if MCOV_PF_TRIM == 2
+            // only the robot's own {free, obst} runs (the state that comes from DRAM); the union plane and the
+            // truth planes are left to the band-row loop
+#elif MCOV_PF_TRIM == 1
+            // the sensor rows of a 1-bit plane are (2R+1) * 4 B: one prefetch per run, the rare run that crosses a
+            // 128-byte line takes its miss in the band-row loop
+            if (do_sense && s >= ((yi - R) >> 5) && s <= ((yi + R) >> 5)) {
+                prefetch_l1(vis_g + vis_off + s * Wp + xi);
+                prefetch_l1(wall_g + map_off + s * Wp + xi);
+                if (!LIDAR) prefetch_l1(tpos_g + map_off + s * Wp + xi);
+            }
+#else
             if (do_sense && s >= ((yi - R) >> 5) && s <= ((yi + R) >> 5)) {
                 const int xc = max(xi - R, 0), xd = min(xi + R, W - 1);
                 prefetch_l1(vis_g + vis_off + s * Wp + xc);
@@ -415,6 +430,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     prefetch_l1(tpos_g + map_off + s * Wp + xd);
                 }
             }
+#endif
         }
     }
     if (do_sense) {
