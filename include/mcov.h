@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define MCOV_ABI_VERSION 7
+#define MCOV_ABI_VERSION 8
 #define MCOV_MAX_ROBOTS 32       /* base-4 joint actions live in an int64: 31 digits; lanes: 32 */
 #define MCOV_MAX_RADIUS 15       /* sensor range, egoradius, mini_map_rad: windows fit 32 bits  */
 #define MCOV_MAX_LASERS 1024
@@ -200,6 +200,27 @@ int mcov_reset(mcov_env* env, const uint8_t* mask_dev, const int32_t* map_idx_de
 int mcov_step(mcov_env* env, const void* actions_dev, int action_format, float* obs_out_dev,
               float* reward_out_dev, double* reward64_out_dev, uint8_t* done_out_dev,
               double* stats_out_dev, void* stream);
+
+/* mcov_step with its launch scratch in a static device array instead of the state arena.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot let a library near the allocator
+ * on the step path (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments, outputs and bits as mcov_step.  It calls no cudaMalloc / cudaFree or allocating routine: the
+ * per-CTA episode-statistics rows and the CTA arrival counter of the launch live in a file-scope
+ * `static __device__` array of MCOV_STATIC_SCRATCH_MAX_ROWS * MCOV_STATS_LEN * 8 + 256 bytes (128 KiB + 256 B) that every
+ * GPU loading the library holds until the process exits; its device address is resolved with cudaGetSymbolAddress
+ * once per device, on the first call with that device current (make that first call outside a graph capture).
+ * Limits, each refused with a message: DecGridRL handles without map_sharing / dist_reward / dijkstra_input /
+ * mini_map_rad (those steps take further launches with arena scratch) -> MCOV_ERR_BAD_CONFIG; a batch whose step
+ * launch can use more than MCOV_STATIC_SCRATCH_MAX_ROWS CTAs -> MCOV_ERR_BAD_CONFIG; a handle of another device than
+ * the current one -> MCOV_ERR_STATE.
+ * The array is shared by EVERY call on a device, whatever the handle or stream, and keeps the last call's contents:
+ * the entry point clears what must start at zero (the counter) on `stream` before the launch, the rows are
+ * overwritten before they are read.  Calls that overlap on the GPU (two streams, two handles, two threads) RACE
+ * on it: serialise them, or use mcov_step, whose scratch is per handle. */
+#define MCOV_STATIC_SCRATCH_MAX_ROWS 2048
+int mcov_step_static_scratch(mcov_env* env, const void* actions_dev, int action_format, float* obs_out_dev,
+                             float* reward_out_dev, double* reward64_out_dev, uint8_t* done_out_dev,
+                             double* stats_out_dev, void* stream);
 
 /* get_egocentric_observations / get_state without stepping (dec_grid_rl.py:312-372,
  * super_grid_rl.py:305-317). */

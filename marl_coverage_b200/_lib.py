@@ -10,7 +10,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmcov_b200.so")
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 MAX_ROBOTS = 32
 MAX_RADIUS = 15
 STATS_LEN = 8
@@ -18,6 +18,7 @@ STATS_LEN = 8
 ENV_DEC, ENV_SUPER = 0, 1
 SENSOR_SQUARE, SENSOR_LIDAR = 0, 1
 ACT_U8_PER_ROBOT, ACT_I64_BASE4 = 0, 1
+STATIC_SCRATCH_MAX_ROWS = 2048                # mcov_step_static_scratch: statistics rows its static array holds
 DONE_TERMINAL, DONE_TRUNCATED = 1, 2          # bits of the done byte mcov_step writes
 
 STATUS_NAMES = {0: "MCOV_OK", -1: "MCOV_ERR_BAD_CONFIG", -2: "MCOV_ERR_NULL", -3: "MCOV_ERR_ALIGN",
@@ -26,7 +27,7 @@ STATUS_NAMES = {0: "MCOV_OK", -1: "MCOV_ERR_BAD_CONFIG", -2: "MCOV_ERR_NULL", -3
 # every symbol include/mcov.h declares (tests check the .so exports exactly these)
 EXPORTS = ("mcov_abi_version", "mcov_last_error", "mcov_plane_geometry", "mcov_create",
            "mcov_destroy", "mcov_set_lidar_beams", "mcov_pack_maps", "mcov_gen_maps", "mcov_set_maps",
-           "mcov_set_cell_values", "mcov_state_layout", "mcov_bind_state", "mcov_obs_shape", "mcov_reset", "mcov_step",
+           "mcov_set_cell_values", "mcov_state_layout", "mcov_bind_state", "mcov_obs_shape", "mcov_reset", "mcov_step", "mcov_step_static_scratch",
            "mcov_observe", "mcov_percent_covered", "mcov_launch_count", "mcov_replay_push",
            "mcov_replay_gather", "mcov_sim_step", "mcov_render_shape", "mcov_render")
 
@@ -88,6 +89,7 @@ def _declare(lib):
     lib.mcov_obs_shape.argtypes = [vp, C.POINTER(C.c_int32 * 5), C.POINTER(C.c_int32)]
     lib.mcov_reset.argtypes = [vp, vp, vp, vp, u64, vp, vp]
     lib.mcov_step.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.mcov_step_static_scratch.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp]
     lib.mcov_observe.argtypes = [vp, vp, vp]
     lib.mcov_percent_covered.argtypes = [vp, vp, vp]
     lib.mcov_replay_push.argtypes = [vp, vp, i32, i64, vp, i32, i32, vp, vp, i32, vp, vp, vp, vp, vp, i64, i64, vp]

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
 #include <new>
 
 #include "mcov_internal.h"
@@ -881,3 +882,109 @@ int mcov_render(mcov_env* env, const int32_t* env_ids_dev, int n_frames, uint8_t
 int64_t mcov_launch_count(const mcov_env* env) { return env ? env->launches : 0; }
 
 }  // extern "C"
+
+// ---- mcov_step_static_scratch: the DecGridRL step with its launch scratch in a static device array ----------------
+// No counterpart in the reference; added for callers that cannot let a library
+// touch the allocator on the step path (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  mcov_step keeps its per-launch scratch — one row of MCOV_STATS_LEN doubles per CTA for the episode
+// statistics fold, and the CTA arrival counter — inside the caller's state arena; this variant keeps them in the array
+// below instead, so the step needs nothing from the arena's scratch region.  Every GPU that loads the library holds the
+// array (MCOV_STATIC_SCRATCH_BYTES = 128 KiB + 256 B) until the process exits.
+//
+// The array's NAME is a host-side stand-in in host code, not a device address: the kernels get the address that
+// cudaGetSymbolAddress returns for the device that is current (resolved once per device, below).
+#define MCOV_STATIC_SCRATCH_BYTES (MCOV_STATIC_SCRATCH_MAX_ROWS * MCOV_STATS_LEN * 8 + 256)
+static __device__ __align__(256) unsigned char g_mcov_static_scratch[MCOV_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::atomic<unsigned char*> g_static_scratch_ptr[kMaxDevices];   // device address of the array, per device ordinal
+
+// Device address of g_mcov_static_scratch on `device`, which must be the current device.  Two threads racing here
+// store the same value.  Allocates nothing (the array is part of the loaded module).
+int static_scratch_address(int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxDevices) return fail(MCOV_ERR_BAD_CONFIG, "device ordinal %d outside [0, %d)", device, kMaxDevices);
+    unsigned char* ptr = g_static_scratch_ptr[device].load(std::memory_order_acquire);
+    if (!ptr) {
+        void* sym = nullptr;
+        cudaError_t ce = cudaGetSymbolAddress(&sym, g_mcov_static_scratch);
+        if (ce != cudaSuccess) return cuda_fail(ce, "cudaGetSymbolAddress(static scratch)");
+        if (!sym) return fail(MCOV_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        ptr = static_cast<unsigned char*>(sym);
+        g_static_scratch_ptr[device].store(ptr, std::memory_order_release);
+    }
+    *out = ptr;
+    return MCOV_OK;
+}
+
+}  // namespace
+
+extern "C" int mcov_step_static_scratch(mcov_env* env, const void* actions_dev, int action_format, float* obs_out_dev,
+                                        float* reward_out_dev, double* reward64_out_dev, uint8_t* done_out_dev,
+                                        double* stats_out_dev, void* stream) {
+    int rc = check_ready(env);
+    if (rc) return rc;
+    const mcov_config& c = env->cfg;
+    if (c.env_type != MCOV_ENV_DEC)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_step_static_scratch: DecGridRL handles only (use mcov_step)");
+    if (c.map_sharing || c.dist_reward || c.dijkstra_input || c.mini_map_rad > 0)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_step_static_scratch: map_sharing / dist_reward / dijkstra_input / mini_map_rad "
+                                         "steps take further launches with arena scratch (use mcov_step)");
+    if (!actions_dev || !obs_out_dev || !reward_out_dev || !done_out_dev)
+        return fail(MCOV_ERR_NULL, "mcov_step_static_scratch: actions/obs/reward/done is NULL");
+    if (action_format != MCOV_ACT_U8_PER_ROBOT && action_format != MCOV_ACT_I64_BASE4)
+        return fail(MCOV_ERR_BAD_CONFIG, "action_format %d", action_format);
+    if (action_format == MCOV_ACT_I64_BASE4 && c.num_robots > 31)
+        return fail(MCOV_ERR_BAD_CONFIG, "base-4 int64 actions hold at most 31 robots");
+    if (action_format == MCOV_ACT_I64_BASE4 && !aligned(actions_dev, 8))
+        return fail(MCOV_ERR_ALIGN, "int64 actions must be 8-byte aligned");
+    if (!aligned(obs_out_dev, 16)) return fail(MCOV_ERR_ALIGN, "obs_out must be 16-byte aligned");
+    if (!aligned(reward_out_dev, 4) || (reward64_out_dev && !aligned(reward64_out_dev, 8)))
+        return fail(MCOV_ERR_ALIGN, "reward buffers misaligned");
+    if (stats_out_dev && !aligned(stats_out_dev, 8)) return fail(MCOV_ERR_ALIGN, "stats_out misaligned");
+    // the size that matters: one statistics row per CTA of the launch
+    const int rows = mcov::dec_launch_grid_max(env);
+    if (rows > MCOV_STATIC_SCRATCH_MAX_ROWS)
+        return fail(MCOV_ERR_BAD_CONFIG, "mcov_step_static_scratch: this batch launches up to %d CTAs, the static scratch holds "
+                                         "%d statistics rows (MCOV_STATIC_SCRATCH_MAX_ROWS); use mcov_step", rows,
+                    MCOV_STATIC_SCRATCH_MAX_ROWS);
+    int cur = -1;
+    cudaError_t ce = cudaGetDevice(&cur);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaGetDevice");
+    if (cur != env->device)
+        return fail(MCOV_ERR_STATE, "mcov_step_static_scratch: handle lives on device %d, current device is %d", env->device, cur);
+    unsigned char* scratch = nullptr;
+    rc = static_scratch_address(cur, &scratch);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned char* counter = scratch + (size_t)MCOV_STATIC_SCRATCH_MAX_ROWS * MCOV_STATS_LEN * 8;
+    // the array keeps whatever the last call (of any handle) left: the rows are overwritten before they are read, the
+    // arrival counter must start at zero
+    ce = cudaMemsetAsync(counter, 0, 256, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaMemsetAsync(static scratch counter)");
+
+    mcov::DecParams p;
+    fill_dec_params(env, p);
+    p.mode = mcov::MODE_STEP;
+    p.actions = actions_dev;
+    p.act_fmt = action_format;
+    p.mask = nullptr;
+    p.mask_from_flags = 0;
+    p.map_idx_in = nullptr;
+    p.start_xy_in = nullptr;
+    p.seed = 0x9E3779B97F4A7C15ull ^ env->seed;                   // as mcov_step: fused auto-resets draw from it
+    p.obs = obs_out_dev;
+    p.reward = reward_out_dev;
+    p.reward64 = reward64_out_dev;
+    p.done = done_out_dev;
+    p.vec_ok = ((p.obs_env_floats * 4) % 16 == 0) && aligned(obs_out_dev, 16);
+    p.phases = mcov::PH_MOVE | mcov::PH_SENSE;
+    p.stats_partial = reinterpret_cast<double*>(scratch);
+    p.stats_out = stats_out_dev;
+    p.counter = reinterpret_cast<unsigned int*>(counter);
+    p.move_scratch = nullptr;                                      // only the dist_reward pipeline uses it (refused above)
+    ce = mcov::launch_dec(env, p, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "dec kernel launch (static scratch)");
+    return MCOV_OK;
+}

@@ -1219,6 +1219,14 @@ cudaError_t launch_dec_t(mcov_env* env, const DecLaunchShape& s, const DecParams
 
 int dec_grid_size(const mcov_env* env) { return dec_shape(env, true).grid; }
 
+// Largest grid a step launch of this handle can use, whichever kernel shape and store path it picks: the number of
+// per-CTA statistics rows a launch may write (mcov_step_static_scratch sizes its check with it).
+int dec_launch_grid_max(const mcov_env* env) {
+    if (want_dec_cta(env)) return dec_cta_grid_size(env);
+    const int a = dec_shape(env, true).grid, b = dec_shape(env, false).grid;
+    return a > b ? a : b;
+}
+
 cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     if (want_dec_cta(env)) return launch_dec_cta(env, p, st);
     const DecLaunchShape s = dec_shape(env, p.vec_ok != 0 && p.obs != nullptr && (p.phases & PH_SENSE));   // a moves-only launch writes no block

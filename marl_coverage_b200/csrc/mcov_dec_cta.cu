@@ -682,6 +682,8 @@ bool want_dec_cta(const mcov_env* env) {
     return c.num_robots >= 2 && (long long)c.num_envs * c.num_robots * 32 <= (long long)env->num_sms * 2048;
 }
 
+int dec_cta_grid_size(const mcov_env* env) { return cta_shape(env).grid; }
+
 cudaError_t launch_dec_cta(mcov_env* env, DecParams& p, cudaStream_t st) {
     const CtaShape s = cta_shape(env);
     p.st_slot_words = 0;

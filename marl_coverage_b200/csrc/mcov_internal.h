@@ -210,6 +210,8 @@ cudaError_t launch_replay_gather(const long long* idx, long long capacity, int B
 cudaError_t launch_sim_lookahead(const SimParams& p, int num_sms, cudaStream_t st);
 cudaError_t launch_render(const RenderParams& p, int num_sms, cudaStream_t st);
 int dec_grid_size(const mcov_env* env);
+int dec_cta_grid_size(const mcov_env* env);             // grid of the CTA-per-env shape (mcov_dec_cta.cu)
+int dec_launch_grid_max(const mcov_env* env);            // upper bound of the statistics rows a Dec step launch writes
 int super_grid_size(const mcov_env* env);
 int64_t super_dt_scratch_bytes(const mcov_env* env);   // 0 when the buffer lives in shared memory
 }  // namespace mcov
