@@ -1148,7 +1148,10 @@ inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
         // CTA size: the one that keeps the most lane groups resident per SM (shared memory is the limit
         // for lidar windows: 2 x 83 kB CTAs hold 64 groups where 5 x 41 kB CTAs hold 80)
         int best = 0;
-        for (int warps = MAX_WARPS; warps >= 1; warps >>= 1) {
+        // lidar handles: 2-warp CTAs, measured on C3 (profiles/r02_ab.jsonl: 8 / 4 / 2 warps 0.1004 / 0.0984 / 0.0968 ms);
+        // the square-sensor step prefers the largest CTA (C5: 8 / 4 / 2 warps 0.1959 / 0.1975 / 0.1984 ms)
+        const int max_warps = (c.sensor_type == MCOV_SENSOR_LIDAR && env->pin_warps < 1) ? 2 : MAX_WARPS;
+        for (int warps = max_warps; warps >= 1; warps >>= 1) {
             if (env->pin_warps >= 1 && warps != env->pin_warps && env->pin_warps <= MAX_WARPS) continue;   // MCOV_DEC_WARPS pins the CTA size
             const int gr = warps * per_warp;
             size_t sm_bytes = s.grp_smem * gr;
