@@ -306,6 +306,7 @@ int mcov_create(const mcov_config* cfg, mcov_env** out) {
     e->pin_team = pin("MCOV_DEC_TEAM");
     e->pin_warps = pin("MCOV_DEC_WARPS");
     e->pin_balance = pin("MCOV_DEC_BALANCE");
+    e->pin_smt = pin("MCOV_DEC_SMT");
     *out = e;
     return MCOV_OK;
 }

@@ -96,6 +96,8 @@ struct GroupSmem {
     uint32_t* winF;      // lidar only: [N*S] sensor-window free hits, window-relative bits
     uint32_t* winO;      //             [N*S] obstacle hits
     uint32_t* wallW;     //             [N*S] truth wall window
+    const uint32_t* mapW;  // Spec::SMT: the shared-memory copy of the truth-map table (wall planes, walkable planes)
+    const uint32_t* mapP;
 };
 
 __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams& p) {
@@ -146,13 +148,21 @@ __device__ __forceinline__ GroupSmem carve(unsigned char* base, const DecParams&
 // second (MODE_RESET) pass of the same lane group (fused auto-reset).
 // Compile-time shape of an env (0 = read the value from DecParams at run time).  The named
 // BASELINE configs get their own instantiation so that loop bounds, divisions and masks fold.
-template <int G_, bool LIDAR_, int CN_, int CR_, int CE_, bool ST_ = false>
+template <int G_, bool LIDAR_, int CN_, int CR_, int CE_, bool ST_ = false, bool SMT_ = false>
 struct Spec {
     static constexpr int G = G_, CN = CN_, CR = CR_, CE = CE_;
     static constexpr bool LIDAR = LIDAR_;
     static constexpr bool FIXED = CN_ > 0;             // then C == 3, N, R, ego are constants
     static constexpr bool ST = ST_;                    // observation blocks leave through the CTA's store warp (TMA bulk stores)
+    // truth-map table resident in shared memory: one 1024-thread CTA per SM stages the whole read-only table (wall +
+    // walkable planes of every map) once per launch with TMA bulk copies; the sensor reads it with shared-memory loads
+    static constexpr bool SMT = SMT_;
+    static constexpr int THREADS = SMT_ ? 1024 : 256, MINB = SMT_ ? 1 : MCOV_DEC_MINB;
 };
+
+// a word of the truth-map table: read-only global memory, or the shared-memory copy (Spec::SMT)
+template <bool SMT>
+__device__ __forceinline__ uint32_t ld_map(const uint32_t* ptr) { return SMT ? *ptr : __ldg(ptr); }
 
 // ---- store-warp hand-over (Spec::ST) -------------------------------------------------------------
 // The lane groups of the pass warps do not write their observation block themselves: a group fills one of
@@ -275,8 +285,8 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
         myv = cur.pos;
     }
     const uint32_t map_off = (uint32_t)map_idx * (uint32_t)PW;
-    const uint32_t* const wall_g = p.wall;
-    const uint32_t* const tpos_g = p.pos;
+    const uint32_t* const wall_g = SP::SMT ? sm.mapW : p.wall;
+    const uint32_t* const tpos_g = SP::SMT ? sm.mapP : p.pos;
 
     // early loads for the bookkeeping at the end of the pass (kept in flight until then)
     int cs0 = 0, fc = 1;
@@ -339,7 +349,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             const int tx = px + (u == 0) - (u == 2);
             const int ty = py + (u == 1) - (u == 3);
             int blocked0 = 1;
-            if (lg < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = get_bit(wall_g + map_off, Wp, tx, ty);
+            if (lg < N && tx >= 0 && tx < W && ty >= 0 && ty < L) blocked0 = (ld_map<SP::SMT>(wall_g + map_off + (ty >> 5) * Wp + tx) >> (ty & 31)) & 1u;
             const uint32_t tv = pack_xy(tx, ty);
             uint32_t pv = myv;
             for (int k = 0; k < N; ++k) {
@@ -423,6 +433,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                 const int xc = max(xi - R, 0), xd = min(xi + R, W - 1);
                 prefetch_l1(vis_g + vis_off + s * Wp + xc);
                 prefetch_l1(vis_g + vis_off + s * Wp + xd);
+                if (SP::SMT) continue;                             // the truth table is in shared memory
                 prefetch_l1(wall_g + map_off + s * Wp + xc);
                 prefetch_l1(wall_g + map_off + s * Wp + xd);
                 if (!LIDAR) {
@@ -564,8 +575,8 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
             // squaresensor.py:15-37 — the footprint is the truth map itself (sees through walls)
             const uint64_t m64 = (uint64_t)low_mask(S) << (sh + rad - R);
             const uint32_t m0 = (uint32_t)m64, m1 = (uint32_t)(m64 >> 32);
-            if (q0) { o0 = __ldg(&wall_g[map_off + w0]) & m0; f0 = __ldg(&tpos_g[map_off + w0]) & m0; }
-            if (q1) { o1 = __ldg(&wall_g[map_off + w0 + Wp]) & m1; f1 = __ldg(&tpos_g[map_off + w0 + Wp]) & m1; }
+            if (q0) { o0 = ld_map<SP::SMT>(&wall_g[map_off + w0]) & m0; f0 = ld_map<SP::SMT>(&tpos_g[map_off + w0]) & m0; }
+            if (q1) { o1 = ld_map<SP::SMT>(&wall_g[map_off + w0 + Wp]) & m1; f1 = ld_map<SP::SMT>(&tpos_g[map_off + w0 + Wp]) & m1; }
             if (single_tool) {                                     // dec_grid_rl.py:233-234
                 const uint64_t c64 = (a2 == rad) ? (1ull << (sh + rad)) : 0ull;
                 f0 = q0 ? (uint32_t)c64 : 0u;
@@ -608,7 +619,7 @@ __device__ __forceinline__ int env_pass(const DecParams& p, const GroupSmem& sm,
                     } else if (single_tool) {
                         add = (x == xj && (yj >> 5) == sk) ? (1u << (yj & 31)) : 0u;
                     } else {
-                        add = __ldg(&tpos_g[map_off + w0 + k * Wp]) & ymask_in_strip(yj, R, S, sk);
+                        add = ld_map<SP::SMT>(&tpos_g[map_off + w0 + k * Wp]) & ymask_in_strip(yj, R, S, sk);
                     }
                     if (k == 0) { comb0 |= add; own0 = own0 && (j > i); }
                     else { comb1 |= add; own1 = own1 && (j > i); }
@@ -795,7 +806,7 @@ MCOV_UNROLL(MCOV_ST_UNROLL)
 }
 
 template <class SP>
-__global__ void __launch_bounds__(MAX_WARPS * 32, MCOV_DEC_MINB)
+__global__ void __launch_bounds__(SP::THREADS, SP::MINB)
 dec_env_kernel(const DecParams p) {
     constexpr int G = SP::G;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -823,6 +834,8 @@ dec_env_kernel(const DecParams p) {
     const int pass_tid = (SP::ST && wid >= sw_first + p.st_warps) ? (int)threadIdx.x - 32 * p.st_warps : (int)threadIdx.x;
     const int gi = store_warp ? 0 : pass_tid / G;
     GroupSmem sm = carve(smem_raw + (size_t)gi * p.grp_smem, p);
+    sm.mapW = reinterpret_cast<const uint32_t*>(smem_raw + p.smt_map_off);
+    sm.mapP = sm.mapW + (size_t)p.n_maps * p.g.PW;
     uint32_t* const bits0 = sm.bits;
     const uint32_t ctr0 = smem_u32(smem_raw + p.st_bar_off);   // uint32 pub[gpc] (blocks published), con[gpc] (consumed)
 
@@ -836,7 +849,28 @@ dec_env_kernel(const DecParams p) {
     if (SP::ST)
         for (int k = threadIdx.x; k < gpc * 2; k += blockDim.x)
             reinterpret_cast<uint32_t*>(smem_raw + p.st_bar_off)[k] = 0u;
+    uint64_t* const map_bar = reinterpret_cast<uint64_t*>(smem_raw + p.smt_bar_off);
+    if (SP::SMT && threadIdx.x == 0) {
+        mbar_init(map_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
+    if (SP::SMT) {
+        // Map staging (TMA): the whole truth-map table — wall planes, then walkable planes, of every map — comes into
+        // shared memory once per launch as bulk async copies of <= 32 kB signalled on one mbarrier; every env this
+        // CTA steps afterwards reads its sensor footprint from there.
+        if (threadIdx.x == 0) {
+            const uint32_t plane_bytes = (uint32_t)p.n_maps * (uint32_t)p.g.PW * 4u;
+            mbar_expect_tx(map_bar, 2u * plane_bytes);
+            for (int t = 0; t < 2; ++t) {
+                const unsigned char* src = reinterpret_cast<const unsigned char*>(t == 0 ? p.wall : p.pos);
+                unsigned char* dst = smem_raw + p.smt_map_off + (size_t)t * plane_bytes;
+                for (uint32_t o = 0; o < plane_bytes; o += 32768u)
+                    bulk_load_g2s(dst + o, src + o, min(32768u, plane_bytes - o), map_bar);
+            }
+        }
+        mbar_wait(map_bar, 0);
+    }
 
     const int gtot = gridDim.x * gpc;
     const int mode = p.mode;
@@ -1066,6 +1100,7 @@ struct DecLaunchShape {
     // store-warp variant (Spec::ST): 0 = off
     int st, slot_words, nbuf, bar_off, stage_off, stage_pitch, nsw;
     int team;                 // lanes that store a block together (>= G)
+    int smt, map_off, map_bar_off;   // truth-map table resident in shared memory (Spec::SMT): byte offsets behind the group areas
 };
 
 inline int pick_group(const mcov_env* env) {
@@ -1184,6 +1219,27 @@ inline DecLaunchShape dec_shape(const mcov_env* env, bool vec_ok) {
         s.threads = groups * s.G;
         s.smem = s.grp_smem * groups;
     }
+    // Truth-map table in shared memory (Spec::SMT): square sensor, direct stores, a batch of several waves, and a table
+    // that fits beside the group areas of one 1024-thread CTA per SM.  MCOV_DEC_SMT=0|1 pins it (read at mcov_create).
+    s.smt = 0; s.map_off = 0; s.map_bar_off = 0;
+    if (!s.st && c.sensor_type != MCOV_SENSOR_LIDAR && env->pin_warps < 1) {
+        const size_t table = (size_t)env->n_maps * env->g.PW * 4 * 2;
+        const int gr = 32 * per_warp;
+        const size_t group_area = ((s.grp_smem * gr + 127) / 128) * 128;
+        const bool fits = group_area + table + 128 <= 220 * 1024 && table % 16 == 0 &&
+                          ((reinterpret_cast<uintptr_t>(env->wall) | reinterpret_cast<uintptr_t>(env->pos)) & 15u) == 0;
+        bool on = false;                                           // default off until the A/B says otherwise
+        if (env->pin_smt >= 0) on = env->pin_smt != 0;
+        if (on && fits) {
+            s.smt = 1;
+            groups = gr;
+            per_sm = 1;
+            s.threads = 1024;
+            s.map_off = (int)group_area;
+            s.map_bar_off = (int)(group_area + table);
+            s.smem = group_area + table + 128;
+        }
+    }
     // store teams: MCOV_DEC_TEAM=8|16|32 pins the lanes per block store (>= G; needs the vector path)
     s.team = s.G;
     if (!s.st && vec_ok && env->pin_team > s.G && env->pin_team <= 32 && (env->pin_team & (env->pin_team - 1)) == 0 &&
@@ -1238,6 +1294,8 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     p.st_warps = s.nsw;
     p.st_rot_div = env->pin_rot == 0 ? 0 : env->num_sms;
     p.store_team = s.team;
+    p.smt_map_off = s.map_off;
+    p.smt_bar_off = s.map_bar_off;
     p.st_bar_off = s.bar_off;
     p.st_stage_off = s.stage_off;
     p.st_stage_pitch = s.stage_pitch;
@@ -1266,7 +1324,13 @@ cudaError_t launch_dec(mcov_env* env, DecParams& p, cudaStream_t st) {
     const bool c2 = plain && !lidar && p.N == 4 && p.R == 2 && p.ego == 5;
     const bool c3 = plain && lidar && p.N == 8 && p.R == 10 && p.ego == 5;
     const bool c4 = plain && !lidar && p.N == 16 && p.R == 2 && p.ego == 5;
-    if (s.st) {
+    if (s.smt) {
+        if (c2 && s.G == 16) err = launch_dec_t<Spec<16, false, 4, 2, 5, false, true>>(env, s, p, st);
+        else if (s.G == 8) err = launch_dec_t<Spec<8, false, 0, 0, 0, false, true>>(env, s, p, st);
+        else if (s.G == 16) err = launch_dec_t<Spec<16, false, 0, 0, 0, false, true>>(env, s, p, st);
+        else err = launch_dec_t<Spec<32, false, 0, 0, 0, false, true>>(env, s, p, st);
+    }
+    else if (s.st) {
         if (c2 && s.G == 8) err = launch_dec_t<Spec<8, false, 4, 2, 5, true>>(env, s, p, st);
         else if (c2 && s.G == 32) err = launch_dec_t<Spec<32, false, 4, 2, 5, true>>(env, s, p, st);
         else if (c3 && s.G == 32) err = launch_dec_t<Spec<32, true, 8, 10, 5, true>>(env, s, p, st);

@@ -688,6 +688,7 @@ cudaError_t launch_dec_cta(mcov_env* env, DecParams& p, cudaStream_t st) {
     const CtaShape s = cta_shape(env);
     p.st_slot_words = 0;
     p.store_team = 0;
+    p.smt_map_off = p.smt_bar_off = 0;
     p.st_nbuf = p.st_warps = p.st_rot_div = p.st_bar_off = p.st_stage_off = p.st_stage_pitch = 0;
     p.rad = p.ego > p.R ? p.ego : p.R;
     p.RW = 2 * p.rad + 1;

@@ -74,6 +74,7 @@ struct DecParams {
     int st_nbuf;              // float32 staging buffers per store warp
     int st_warps;             // store warps per CTA
     int store_team;           // lanes that store an observation block together (>= lanes per env; direct-store path)
+    int smt_map_off, smt_bar_off;   // Spec::SMT: byte offsets of the shared-memory truth-map table and its mbarrier
     int st_rot_div;           // store warp index = (blockIdx / st_rot_div) % 4 (0: the CTA's last warps)
     int st_bar_off, st_stage_off, st_stage_pitch;
 };
@@ -178,8 +179,8 @@ struct mcov_env {
     int debug;                // MCOV_DEBUG at mcov_create (profiling aids; 0 in normal use)
     // tuning / test pins read from the environment once, at mcov_create (-1 = not pinned):
     // MCOV_DEC_GROUP (lanes per env), MCOV_DEC_STORE (store-warp path 0|1), MCOV_DEC_GRID (grid cap),
-    // MCOV_DEC_NBUF (staging buffers per store warp), MCOV_DEC_SW (store warps per CTA), MCOV_DEC_SHAPE (0 lane groups, 1 CTA per env), MCOV_DEC_TMA (CTA shape: 0 plain loads, 1 bulk-copy staging)
-    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma, pin_team, pin_warps, pin_balance;
+    // MCOV_DEC_NBUF (staging buffers per store warp), MCOV_DEC_SW (store warps per CTA), MCOV_DEC_SHAPE (0 lane groups, 1 CTA per env), MCOV_DEC_TMA (CTA shape: 0 plain loads, 1 bulk-copy staging), MCOV_DEC_SMT (lane groups: truth-map table in shared memory)
+    int pin_group, pin_store, pin_grid, pin_nbuf, pin_shape, pin_sw, pin_rot, pin_tma, pin_team, pin_warps, pin_balance, pin_smt;
     size_t dec_smem_configured, super_smem_configured;   // dynamic shared memory opted into on this handle's device
     const void* dec_smem_func;  // ... and for which instantiation (MCOV_DEC_GROUP can change it between launches)
     const double* cell_values;  // Super: float64 [n_maps][W][L] reward of covering a cell, or null (= 1.0)

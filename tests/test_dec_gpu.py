@@ -82,6 +82,23 @@ def test_dec_golden_store_teams(name, group, team, monkeypatch):
     replay_trace_on_gpu(tr, VecDecGridRL, num_envs=150, check_envs=(0, 61, 149))
 
 
+@pytest.mark.parametrize("group", [8, 16, 32])
+@pytest.mark.parametrize("name", [n for n in DEC_TRACES if "lidar" not in n])
+def test_dec_golden_map_table_in_shared_memory(name, group, monkeypatch):
+    """Square-sensor handles can keep the whole read-only truth-map table in shared memory (one 1024-thread CTA per SM
+    stages it once per launch with TMA bulk copies; MCOV_DEC_SMT pins it).  Every non-lidar golden trace must give the
+    same bits; two CTAs loop over 150 envs."""
+    from marl_coverage_b200 import VecDecGridRL
+    from gpu_helpers import replay_trace_on_gpu
+    monkeypatch.setenv("MCOV_DEC_SHAPE", "0")
+    monkeypatch.setenv("MCOV_DEC_GROUP", str(group))
+    monkeypatch.setenv("MCOV_DEC_SMT", "1")
+    monkeypatch.setenv("MCOV_DEC_GRID", "2")
+    tr = Trace.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    tol = 1e-6 if tr.config["mini_map_rad"] > 0 else 0.0
+    replay_trace_on_gpu(tr, VecDecGridRL, num_envs=150, check_envs=(0, 61, 149), obs_tol=tol)
+
+
 @pytest.mark.parametrize("tma", [0, 1])
 @pytest.mark.parametrize("name", DEC_TRACES)
 def test_dec_golden_cta_per_env_shape(name, tma, monkeypatch):

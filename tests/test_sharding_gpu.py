@@ -48,10 +48,12 @@ def test_logical_shards_equal_single_batch(shards):
 
 
 @pytest.mark.parametrize("group,variant", [(8, "MCOV_DEC_STORE=1"), (32, "MCOV_DEC_STORE=1"), (8, "MCOV_DEC_TEAM=16"),
-                                           (8, "MCOV_DEC_TEAM=32"), (16, "MCOV_DEC_TEAM=32"), (8, "MCOV_DEC_SHAPE=1")])
+                                           (8, "MCOV_DEC_TEAM=32"), (16, "MCOV_DEC_TEAM=32"), (8, "MCOV_DEC_SHAPE=1"),
+                                           (8, "MCOV_DEC_SMT=1"), (16, "MCOV_DEC_SMT=1"), (32, "MCOV_DEC_SMT=1")])
 def test_kernel_variants_equal_plain_path_with_auto_reset(group, variant, monkeypatch):
     """The variants of the DecGridRL step kernel — store warp (bit-stream slots -> TMA bulk stores), store teams
-    (16 / 32 lanes write a block together), CTA-per-env shape — against the plain lane-group path on the same seeded
+    (16 / 32 lanes write a block together), CTA-per-env shape, truth-map table staged into shared memory by TMA (one
+    1024-thread CTA per SM) — against the plain lane-group path on the same seeded
     batch with fused auto-resets: a finished env re-runs its pass in RESET mode before its block is written.  Three
     CTAs loop over the batch (slots and teams are reused many times; the batch size leaves some teams incomplete)."""
     import torch
